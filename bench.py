@@ -1,0 +1,327 @@
+#!/usr/bin/env python
+"""bench.py — throughput of the Ink-Simulation hot path (System::solve) on B200.
+
+One "step" = one System::solve (MAC water-grid update + RK2 particle update, reference src/inkSolver.cpp:5-9) on
+synthetic input.  Default workload at N=1 = BASELINE.json configs[2]: 10M particles (uniform, UNSORTED input order)
+on a 128x256x128 MAC grid, fp32.  Prints ONE JSON line (see the contract in the task statement):
+  value      : particle RK2 updates/s over whole steps (state resident in HBM)
+  e2e        : same, through the host-facing call: pinned-host positions in (H2D) -> solve -> positions out (D2H) every step
+  roofline   : dominant kernel's algorithmic bytes / CUDA-event time vs MEASURED_PEAKS.json
+  cpu_baseline: the CPU oracle port (OpenMP, all host cores) on a bounded sample of the same workload
+`--impl reference` times the CPU implementation (compiled reference where it can run the config, else the oracle port).
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+CONFIGS = {
+    "c1": dict(dims=(8, 25, 8), particles=10_000, cloud="box"),
+    "c2": dict(dims=(20, 45, 20), particles=100_000, cloud="box"),
+    "c3": dict(dims=(128, 256, 128), particles=10_000_000, cloud="uniform"),
+    "c4": dict(dims=(256, 256, 256), particles=100_000_000, cloud="uniform"),
+}
+RENDER_DT = 0.35  # src/main.cpp:25
+
+
+def make_particles(dims, n, cloud, seed=0x1234):
+    rng = np.random.default_rng(seed)
+    X, Y, Z = dims
+    if cloud == "box":  # initParticles box, src/system.cpp:102-104
+        lo = np.array([X / 2 - X / 5, Y - 1.5, Z / 2 - Z / 3])
+        hi = np.array([X / 2 + X / 5, Y - 1.0, Z / 2 + Z / 3])
+    else:
+        lo = np.array([0.5, 0.5, 0.5])
+        hi = np.array([X - 0.5, Y - 0.5, Z - 0.5])
+    out = np.empty((n, 3), np.float32)
+    chunk = 4_000_000
+    for s in range(0, n, chunk):
+        e = min(n, s + chunk)
+        out[s:e] = (lo + rng.random((e - s, 3)) * (hi - lo)).astype(np.float32)
+    return out
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, dev):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(dev), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f.read().splitlines():
+            parts = [x.strip() for x in line.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0])); mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for nm, val in zip(names, parts[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        os.unlink(self.f.name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def cpu_port_sample(dims, pos, steps, warm_state=None):
+    """The CPU oracle (OpenMP restatement of the reference, oracle/ink_oracle.cpp) on the same workload; returns
+    (seconds per step, threads)."""
+    import oracle
+
+    oracle.build()
+    O = oracle.OracleSystem(*dims, dtype=np.float32)
+    O.set_particles(pos)
+    if warm_state is not None:
+        O.set_velocity(*warm_state)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        O.solve(RENDER_DT)
+    dt = (time.perf_counter() - t0) / steps
+    return dt, os.cpu_count()
+
+
+def run_reference_arm(args, cfg, rank, world):
+    """--impl reference: the CPU implementation on the host cores.  The compiled reference (hash-map grid + SparseLU)
+    cannot run grids beyond ~32x64x32, so for c3/c4 the OpenMP oracle port stands in (kind: "port")."""
+    if rank != 0:
+        return
+    import oracle
+
+    oracle.build()
+    dims, n = cfg["dims"], cfg["particles"]
+    use_ref = oracle.have_ref() and dims[0] * dims[1] * dims[2] <= 20000 and dims[0] == dims[2]
+    sample_n = n if use_ref else min(n, args.cpu_particles)
+    pos = make_particles(dims, sample_n, cfg["cloud"])
+    if use_ref:
+        T = oracle.RefSystem(*dims)
+        kind, cores = "reference", 1
+    else:
+        T = oracle.OracleSystem(*dims, dtype=np.float32)
+        kind, cores = "port", os.cpu_count()
+    T.set_particles(pos)
+    for _ in range(args.warmup):
+        T.solve(RENDER_DT)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        T.solve(RENDER_DT)
+    sec = (time.perf_counter() - t0) / args.steps
+    val = sample_n / sec
+    sample = f"{args.steps} System::solve steps, grid {dims[0]}x{dims[1]}x{dims[2]}, {sample_n} particles ({cfg['cloud']})"
+    line = {
+        "impl": "reference", "metric": "particle_rk2_updates_per_s", "value": val, "unit": "particle-updates/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.config, "grid": list(dims), "particles": sample_n, "cloud": cfg["cloud"]},
+        "mac_cell_steps_per_s": dims[0] * dims[1] * dims[2] / sec,
+        "cpu_baseline": {"value": val, "unit": "particle-updates/s", "cores": cores, "kind": kind, "sample": sample},
+        "e2e": {"value": val, "unit": "particle-updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--config", default="c3", choices=sorted(CONFIGS))
+    ap.add_argument("--particles", type=int, default=None)
+    ap.add_argument("--arith", default="strict", choices=["strict", "fast"])
+    ap.add_argument("--dtype", default="f32", choices=["f32", "f64"])
+    ap.add_argument("--cg-rtol", type=float, default=1e-6)
+    ap.add_argument("--resort", type=int, default=16)
+    ap.add_argument("--cpu-steps", type=int, default=1, help="oracle steps for cpu_baseline (0 = skip)")
+    ap.add_argument("--cpu-particles", type=int, default=10_000_000)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-kernels", action="store_true", help="skip the per-kernel roofline micro-timings")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    cfg = dict(CONFIGS[args.config])
+    if args.particles:
+        cfg["particles"] = args.particles
+    if args.impl == "reference":
+        run_reference_arm(args, cfg, rank, world)
+        return
+
+    import torch
+
+    from ink_simulation_b200 import System
+
+    if world > 1:
+        raise SystemExit("multi-GPU bench arm not wired yet in this revision")
+    torch.cuda.set_device(local)
+    dims, n = cfg["dims"], cfg["particles"]
+    ncell = dims[0] * dims[1] * dims[2]
+    dtype = np.float32 if args.dtype == "f32" else np.float64
+    rbytes = 4 if args.dtype == "f32" else 8
+    pos_host = torch.from_numpy(make_particles(dims, n, cfg["cloud"])).pin_memory()
+    out_host = torch.empty_like(pos_host).pin_memory()
+
+    S = System(*dims, dtype=dtype, arith=args.arith, device=local, cg_rtol=args.cg_rtol, resort_interval=args.resort)
+    S.set_particles(pos_host)
+    for _ in range(max(3, args.warmup)):
+        S.solve(RENDER_DT)
+    torch.cuda.synchronize()
+
+    # ---- timed region: K whole steps, state resident in HBM -------------------------------------------
+    st0 = S.stats()
+    sampler = ClockSampler(local)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    phase_acc = {}
+    iters = []
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(args.steps):
+        S.solve(RENDER_DT)
+        iters.append(S.stats().cg_iters)
+    e1.record()
+    torch.cuda.synchronize()
+    ms_total = e0.elapsed_time(e1)
+    clocks = sampler.stop()
+    st1 = S.stats()
+    ms_step = ms_total / args.steps
+    value = n / (ms_step * 1e-3)
+    # phase split of the LAST timed step (CUDA events recorded inside ink_step on the launching stream)
+    phase_acc = S.phase_ms()
+
+    # ---- e2e: host positions in -> solve -> host positions out, every step ------------------------------
+    e2e = None
+    if not args.no_e2e:
+        S.get_particles(0, out_pos=out_host)
+        torch.cuda.synchronize()
+        k2 = max(3, args.steps // 4)
+        e0.record()
+        for _ in range(k2):
+            S.set_particles(out_host)             # H2D from pinned memory (+ re-binning)
+            S.solve(RENDER_DT)
+            S.get_particles(0, out_pos=out_host)  # D2H into pinned memory, caller's particle order
+        e1.record()
+        torch.cuda.synchronize()
+        ms_e2e = e0.elapsed_time(e1) / k2
+        e2e = {"value": n / (ms_e2e * 1e-3), "unit": "particle-updates/s", "ms_per_step": ms_e2e,
+               "h2d_bytes_per_step": n * 12, "d2h_bytes_per_step": n * 12}
+
+    # ---- per-kernel roofline micro-timings (CUDA events, same process, after the timed region) -------------
+    peak, peak_src = peaks()
+    kernels = {}
+    if not args.no_kernels:
+        # K8 particles_rk2 on the current (developed) field, re-binned first; 36 B/particle (fp32) + field once
+        S.resort_particles()
+        dt = S.stats().dt
+        torch.cuda.synchronize()
+        reps = 10
+        e0.record()
+        for _ in range(reps):
+            S._ck(S.L.ink_particles(S.h, 0.0))  # dt = 0: same memory traffic and arithmetic, particles stay binned
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / reps
+        alg = (9 * rbytes) * n + 3 * rbytes * ncell
+        kernels["k_particles_rk2"] = {"ms": ms, "alg_bytes": alg, "gbs": alg / ms / 1e6, "frac": alg / ms / 1e6 / peak}
+        # CG iteration pair (k_cg_dir_matvec + k_cg_update): 10*R B/cell/iteration; fixed 100 iterations, tolerance off
+        S2 = System(*dims, dtype=dtype, device=local, cg_rtol=0.0, cg_max_iters=100, cg_check_every=100)
+        b = torch.randn(dims, dtype=torch.float32 if rbytes == 4 else torch.float64, device="cuda")
+        pout = torch.empty_like(b)
+        import ctypes as C
+
+        S2._ck(S2.L.ink_poisson_solve(S2.h, C.c_void_p(b.data_ptr()), C.c_void_p(pout.data_ptr()), 32 if rbytes == 4 else 64))
+        torch.cuda.synchronize()
+        e0.record()
+        S2._ck(S2.L.ink_poisson_solve(S2.h, C.c_void_p(b.data_ptr()), C.c_void_p(pout.data_ptr()), 32 if rbytes == 4 else 64))
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        it = S2.stats().cg_iters
+        alg = 10 * rbytes * ncell * it
+        kernels["cg_iteration"] = {"ms_per_iter": ms / max(it, 1), "iters": it, "alg_bytes_per_iter": 10 * rbytes * ncell,
+                                   "gbs": alg / ms / 1e6, "frac": alg / ms / 1e6 / peak,
+                                   "note": "includes conversion/transposes of b and p (2 passes) around 100 iterations"}
+        S2.close()
+
+    # dominant kernel of the step = the CG pair (pressure phase) unless particles take longer
+    cg_ms = phase_acc.get("pressure", 0.0)
+    part_ms = phase_acc.get("particles", 0.0)
+    last_iters = iters[-1] if iters else 0
+    if cg_ms >= part_ms and last_iters > 0:
+        alg = 10 * rbytes * ncell * last_iters + (4 + 3 + 7 + 2) * rbytes * ncell  # + rhs, init, p=q+patm, gradient subtract
+        roof = {"kernel": "k_cg_dir_matvec+k_cg_update (pressure phase)", "bound": "hbm", "achieved": alg / cg_ms / 1e6, "peak": peak,
+                "unit": "GB/s", "frac": alg / cg_ms / 1e6 / peak, "traffic": None, "peak_source": peak_src,
+                "alg_bytes_per_launch_pair": 10 * rbytes * ncell, "cg_iters": last_iters}
+    else:
+        alg = (9 * rbytes) * n + 3 * rbytes * ncell
+        roof = {"kernel": "k_particles_rk2", "bound": "hbm", "achieved": alg / max(part_ms, 1e-9) / 1e6, "peak": peak, "unit": "GB/s",
+                "frac": alg / max(part_ms, 1e-9) / 1e6 / peak, "traffic": None, "peak_source": peak_src}
+
+    cpu = None
+    if args.cpu_steps > 0:
+        sample_n = min(n, args.cpu_particles)
+        u, v, w = S.get_velocity()
+        sec, cores = cpu_port_sample(dims, pos_host.numpy()[:sample_n], args.cpu_steps, warm_state=(u, v, w))
+        cpu = {"value": sample_n / sec, "unit": "particle-updates/s", "cores": cores, "kind": "port",
+               "sample": f"{args.cpu_steps} System::solve step(s) of the same workload ({sample_n} particles, grid {dims}) "
+                         f"from the GPU's developed velocity field; OpenMP oracle port, exact DST Poisson solve",
+               "ms_per_step": sec * 1e3, "mac_cell_steps_per_s": ncell / sec}
+
+    water_ms = sum(phase_acc.get(k, 0.0) for k in ("dt", "advect", "forces", "viscosity", "pressure", "vorticity"))
+    line = {
+        "metric": "particle_rk2_updates_per_s", "value": value, "unit": "particle-updates/s", "n_gpus": 1, "steps": args.steps,
+        "warmup": max(3, args.warmup), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": args.dtype, "data": "synthetic",
+        "config": {"workload": f"{args.config}: {n} particles ({cfg['cloud']}, unsorted input), {dims[0]}x{dims[1]}x{dims[2]} MAC grid, "
+                               f"full System::solve per step", "arith": args.arith, "cg_rtol": args.cg_rtol,
+                   "resort_interval": args.resort, "l2": "inputs larger than L2 (particles 360 MB + CG vectors 84 MB per pass)"},
+        "mac_cell_steps_per_s": ncell / (ms_step * 1e-3),
+        "mac_only_cell_steps_per_s": ncell / (water_ms * 1e-3) if water_ms > 0 else None,
+        "particles_only_updates_per_s": n / (part_ms * 1e-3) if part_ms > 0 else None,
+        "cg_iters_per_step": {"mean": float(np.mean(iters)), "min": int(min(iters)), "max": int(max(iters))},
+        "phase_ms_last_step": phase_acc,
+        "roofline": roof, "kernels": kernels, "cpu_baseline": cpu, "e2e": e2e,
+        "gpu_launches": int(st1.kernel_launches - st0.kernel_launches), "resorts_in_timed_region": int(st1.resorts - st0.resorts),
+        "clocks": clocks,
+    }
+    print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,120 @@
+/*
+ * ink_capi.h — C ABI of the B200-native Ink-Simulation hot path (libinkb200.so).
+ *
+ * The reference (zhang-tianran/Ink-Simulation) has no FFI; its seam is the C++ class `System`
+ * (src/system.h:70-138).  This ABI sits *underneath* a drop-in `System` (host/system.h in this
+ * repo): every entry point names the reference member it replaces.  Plain pointers and sizes only;
+ * no C++/Eigen/torch types cross the boundary.  All calls return 0 on success, non-zero on error
+ * (message via ink_last_error).  One ctx = one host thread = one CUDA device; all work is ordered
+ * on the ctx's stream.  There is NO CPU fallback: ink_create fails if no sm_100 device is present.
+ *
+ * Array conventions (identical to oracle/ and the compiled-reference shim):
+ *   grid fields  : dense (X, Y, Z) C-order, z fastest: idx = (i*Y + j)*Z + k
+ *   particles    : AoS xyz, N x 3 (the layout of Particle::position / ::velocity, src/system.h:52-60)
+ *   host_dtype   : 32 = float arrays, 64 = double arrays (independent of the ctx's compute precision)
+ * Pointers may be host (pageable or pinned) or device pointers; the library detects which.
+ */
+#ifndef INK_CAPI_H
+#define INK_CAPI_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct ink_ctx ink_ctx;
+
+enum { INK_ARITH_STRICT = 0, INK_ARITH_FAST = 1 };
+enum { INK_FIELD_OLD = 0, INK_FIELD_CURR = 1, INK_FIELD_CURL = 2 };
+enum { INK_PCG_NONE = 0, INK_PCG_MG = 1 };
+
+/* Run-time copy of the reference's compile-time globals (src/system.h:13-38) + solver knobs. */
+typedef struct ink_params {
+    int32_t X, Y, Z;        /* WATERGRID_X/Y/Z            src/system.h:15-17 */
+    float cell_dim;         /* CELL_DIM                   :22 */
+    float density;          /* DENSITY                    :25 */
+    float k_vort;           /* K_VORT                     :27 */
+    float viscosity;        /* VISCOSITY                  :30 */
+    float p_atm;            /* ATMOSPHERIC_PRESSURE       :31 */
+    float gravity[3];       /* gravity                    :34 */
+    float k_cfl;            /* K_CFL                      :36 */
+    float dt_min;           /* MIN_TIMESTEP               :37 */
+    float dt_max;           /* MAX_TIMESTEP               :38 */
+    int32_t buffer_size;    /* BUFFER_SIZE                :23 */
+    int32_t precision;      /* 32 (reference arithmetic) or 64 */
+    int32_t arith;          /* INK_ARITH_STRICT: reference operation order, no FMA contraction (bit-identical to the
+                               compiled reference in fp32); INK_ARITH_FAST: FMA lerp form in the particle kernel */
+    int32_t device;         /* CUDA device ordinal */
+    /* Pressure solve: replaces Eigen::SparseLU (src/system.h:105, src/waterSolver.cpp:259,279) by matrix-free CG */
+    double  cg_rtol;        /* stop when ||r||_2 <= cg_rtol * ||b||_2 */
+    int32_t cg_max_iters;
+    int32_t cg_check_every; /* iterations between host convergence polls */
+    int32_t cg_warm_start;  /* 1: start from the previous step's pressure */
+    int32_t cg_precond;     /* INK_PCG_NONE | INK_PCG_MG */
+    int32_t resort_interval;/* re-bin particles by cell every this many particle updates (0 = never) */
+    /* multi-GPU (one process per GPU).  world_size==1: single device. */
+    int32_t rank, world_size;
+    uint8_t nccl_id[128];   /* ncclUniqueId from ink_nccl_unique_id on rank 0, broadcast by the caller */
+} ink_params;
+
+typedef struct ink_stats {
+    double  dt;             /* last time step */
+    int32_t cg_iters;       /* iterations of the last pressure solve */
+    double  cg_rel_residual;/* ||r||/||b|| at exit (recurrence residual) */
+    int32_t advect_skipped; /* 1 if the convection phase was proven to be the identity and skipped */
+    int64_t steps;          /* ink_step calls so far */
+    int64_t resorts;        /* particle re-binnings so far */
+    int64_t kernel_launches;/* kernels launched by this ctx so far */
+} ink_stats;
+
+void ink_default_params(ink_params* p);                 /* the committed values of src/system.h:13-38 */
+int  ink_nccl_unique_id(uint8_t out[128]);
+int  ink_create(const ink_params* p, ink_ctx** out);    /* System::System + initWaterGrid (src/system.cpp:8,40-60); no LU setup */
+void ink_destroy(ink_ctx* c);
+const char* ink_last_error(const ink_ctx* c);           /* c may be NULL: last create error */
+int  ink_sync(ink_ctx* c);
+
+/* ---- state in / out ------------------------------------------------------------------------ */
+/* m_ink[drop] = particles (src/system.h:115; initFromFile-style seeding src/system.cpp:117-148).  vel may be NULL (zero).
+ * Multi-GPU: every rank passes the FULL drop; each rank keeps its contiguous index shard. */
+int  ink_set_particles(ink_ctx* c, int drop, const void* pos_xyz, const void* vel_xyz, int64_t n, int host_dtype);
+int  ink_num_drops(const ink_ctx* c);
+int64_t ink_num_particles(const ink_ctx* c, int drop);  /* local shard size under multi-GPU */
+/* getInkParticles() (src/system.cpp:151-153): original particle order; either pointer may be NULL. */
+int  ink_get_particles(ink_ctx* c, int drop, void* pos_xyz, void* vel_xyz, int host_dtype);
+/* oldVelocity = currVelocity = (u,v,w)  (Cell, src/system.h:41-50) */
+int  ink_set_velocity(ink_ctx* c, const void* u, const void* v, const void* w, int host_dtype);
+/* getWaterGrid() (src/system.cpp:155-157) as three dense arrays; which = INK_FIELD_* */
+int  ink_get_field(ink_ctx* c, int which, void* u, void* v, void* w, int host_dtype);
+int  ink_get_pressure(ink_ctx* c, void* p, int host_dtype);
+int  ink_set_pressure(ink_ctx* c, const void* p, int host_dtype);   /* warm-start seed / pressure_given tests */
+int  ink_get_mark(ink_ctx* c, uint8_t* mark);           /* force mask of the last forces phase */
+int  ink_get_divergence(ink_ctx* c, void* div, int host_dtype);  /* getDivergence on oldVelocity, src/systemHelpers.cpp:30-43 */
+int  ink_sample_velocity(ink_ctx* c, const void* pos_xyz, int64_t n, void* out_xyz, int host_dtype); /* getVelocity :110-115 */
+
+/* ---- the hot path --------------------------------------------------------------------------- */
+/* System::solve (src/inkSolver.cpp:5-9): updateWaterGrid then updateParticles; *dt_out = returned time step. */
+int  ink_step(ink_ctx* c, double time_to_next_render, double* dt_out);
+/* Per-phase hooks, each = the phase followed by the reference's `old = curr` sweep (src/waterSolver.cpp:41-96). */
+int  ink_calc_dt(ink_ctx* c, double time_to_next_render, double* dt_out);  /* calcTimeStep      src/waterSolver.cpp:13-38 */
+int  ink_advect(ink_ctx* c, double dt);                 /* applyConvection    :109-128 */
+int  ink_forces(ink_ctx* c, double dt);                 /* applyExternalForces:158-191 */
+int  ink_viscosity(ink_ctx* c, double dt);              /* applyViscosity     :225-238 */
+int  ink_pressure_rhs(ink_ctx* c, double dt, void* b_out, int host_dtype); /* RHS of calculatePressure :264-278 (no state change) */
+int  ink_pressure(ink_ctx* c, double dt);               /* applyPressure      :284-296 (RHS + solve + gradient subtract) */
+int  ink_pressure_given_p(ink_ctx* c, double dt);       /* gradient subtract with the pressure set by ink_set_pressure */
+int  ink_poisson_solve(ink_ctx* c, const void* b, void* p, int host_dtype); /* llt.solve(b) :279 for arbitrary b */
+int  ink_vorticity(ink_ctx* c, double dt);              /* applyVorticity     :203-222 */
+int  ink_velocity_field_update(ink_ctx* c, double dt);  /* updateVelocityField:41-96 */
+int  ink_particles(ink_ctx* c, double dt);              /* updateParticles    src/inkSolver.cpp:44-84 */
+int  ink_resort_particles(ink_ctx* c);                  /* re-bin now (no reference equivalent; layout only) */
+
+int  ink_get_stats(ink_ctx* c, ink_stats* out);
+/* Device-time of every phase of the last ink_step in ms: dt, advect, forces, viscosity, pressure, vorticity, particles, resort */
+int  ink_get_phase_ms(ink_ctx* c, float out[8]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* INK_CAPI_H */

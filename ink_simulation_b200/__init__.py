@@ -1,0 +1,9 @@
+"""ink_simulation_b200 — B200-native (sm_100a) implementation of Ink-Simulation's per-timestep hot path
+(System::solve: MAC water-grid update + RK2 ink-particle update) behind the reference's System / InkSim interface.
+
+Layout:  csrc/  CUDA kernels + the C ABI (include/ink_capi.h -> libinkb200.so)
+         host/  C++ drop-in `System` / `InkSim` over the C ABI (the reference is C++)
+         system.py / inksim.py  Python mirror of the same interface for tests and bench.py
+"""
+from ._capi import LIB_PATH, load  # noqa: F401
+from .system import InkError, Params, System  # noqa: F401

@@ -1,0 +1,777 @@
+// capi.cu — the C ABI of include/ink_capi.h: context, device memory, phase sequencing of System::solve
+// (reference src/inkSolver.cpp:5-9, src/waterSolver.cpp:7-96) over the kernels in *_kernels.cuh / cg.cuh.
+// There is deliberately no CPU code path: without a CUDA device ink_create fails.
+#include "../../include/ink_capi.h"
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "cg.cuh"
+#include "common.cuh"
+#include "grid_kernels.cuh"
+#include "particle_kernels.cuh"
+
+namespace ink {
+
+static thread_local std::string g_create_error;
+
+#define CK(call)                                                                                         \
+    do {                                                                                                 \
+        cudaError_t e_ = (call);                                                                         \
+        if (e_ != cudaSuccess) {                                                                         \
+            char buf_[512];                                                                              \
+            snprintf(buf_, sizeof buf_, "%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+            this->err = buf_;                                                                            \
+            return 1;                                                                                    \
+        }                                                                                                \
+    } while (0)
+
+#define LAUNCH(kern, grid, block, ...)                     \
+    do {                                                   \
+        kern<<<(grid), (block), 0, stream>>>(__VA_ARGS__); \
+        ++stats.kernel_launches;                           \
+    } while (0)
+
+static inline unsigned int nblk(long long n, int b = 256) { return (unsigned int)((n + b - 1) / b); }
+
+struct CtxBase {
+    ink_params P;
+    std::string err;
+    ink_stats stats{};
+    cudaStream_t stream = 0;
+    virtual ~CtxBase() {}
+    virtual int init() = 0;
+    virtual int set_particles(int drop, const void* pos, const void* vel, int64_t n, int dt) = 0;
+    virtual int num_drops() const = 0;
+    virtual int64_t num_particles(int drop) const = 0;
+    virtual int get_particles(int drop, void* pos, void* vel, int dt) = 0;
+    virtual int set_velocity(const void* u, const void* v, const void* w, int dt) = 0;
+    virtual int get_field(int which, void* u, void* v, void* w, int dt) = 0;
+    virtual int get_pressure(void* p, int dt) = 0;
+    virtual int set_pressure(const void* p, int dt) = 0;
+    virtual int get_mark(uint8_t* m) = 0;
+    virtual int get_divergence(void* d, int dt) = 0;
+    virtual int sample_velocity(const void* pos, int64_t n, void* out, int dt) = 0;
+    virtual int step(double ttnr, double* dt_out) = 0;
+    virtual int calc_dt(double ttnr, double* dt_out) = 0;
+    virtual int advect(double dt) = 0;
+    virtual int forces(double dt) = 0;
+    virtual int viscosity(double dt) = 0;
+    virtual int pressure_rhs(double dt, void* b, int hd) = 0;
+    virtual int pressure(double dt) = 0;
+    virtual int pressure_given_p(double dt) = 0;
+    virtual int poisson_solve(const void* b, void* p, int hd) = 0;
+    virtual int vorticity(double dt) = 0;
+    virtual int velocity_field_update(double dt) = 0;
+    virtual int particles(double dt) = 0;
+    virtual int resort() = 0;
+    virtual int phase_ms(float out[8]) = 0;
+};
+
+template <class Real>
+struct Ctx final : CtxBase {
+    Grid g{};
+    Consts<Real> C{};
+    // MAC grid state (struct Cell, src/system.h:41-50) as SoA; vel[cur] is the committed (old == curr) field
+    Real* vel[2][3] = {{nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr}};
+    int cur = 0;
+    Real* curl[3] = {nullptr, nullptr, nullptr};
+    Real *pres = nullptr, *q = nullptr, *rhs = nullptr, *cg_r = nullptr, *cg_d[2] = {nullptr, nullptr}, *cg_w = nullptr;
+    bool have_q = false;
+    CgScal* S = nullptr;
+    CgScal* hS = nullptr;  // pinned mirror of the scalar head
+    uint8_t *seed = nullptr, *mark = nullptr;
+    unsigned int* d_scal = nullptr;  // [0] max speed bits, [1] oob particle count
+    unsigned int* h_scal = nullptr;  // pinned
+    bool maxv_valid = false, seed_valid = false;
+    // phantom map cells created by out-of-grid particles (Q8): all carry the same accumulated dt*g
+    bool have_phantom = false, oob_now = false;
+    Real phantom_v[3] = {0, 0, 0};
+    // particles (m_ink, src/system.h:115): all drops concatenated, binned by cell
+    Particles<Real> part[2]{};
+    int pcur = 0;
+    long long pcap = 0, np = 0;
+    std::vector<long long> drop_off, drop_n;
+    uint32_t *bin_count = nullptr, *bin_key = nullptr, *bin_rank = nullptr;
+    std::vector<uint32_t*> scan_lvl;  // tile sums per level
+    std::vector<long long> scan_n;
+    long long since_sort = 0;
+    // staging for host <-> device conversion
+    void* stage = nullptr;
+    size_t stage_bytes = 0;
+    cudaEvent_t ev[10]{};
+    bool ev_valid = false;
+
+    ~Ctx() override {
+        for (auto& b : vel)
+            for (auto& p : b) cudaFree(p);
+        for (auto& p : curl) cudaFree(p);
+        cudaFree(pres); cudaFree(q); cudaFree(rhs); cudaFree(cg_r); cudaFree(cg_d[0]); cudaFree(cg_d[1]); cudaFree(cg_w);
+        cudaFree(S); cudaFreeHost(hS); cudaFree(seed); cudaFree(mark); cudaFree(d_scal); cudaFreeHost(h_scal);
+        free_particles();
+        cudaFree(bin_count);
+        for (auto p : scan_lvl) cudaFree(p);
+        cudaFree(stage);
+        for (auto& e : ev)
+            if (e) cudaEventDestroy(e);
+    }
+    void free_particles() {
+        for (auto& pp : part) {
+            for (auto& p : pp.p) { cudaFree(p); p = nullptr; }
+            for (auto& p : pp.v) { cudaFree(p); p = nullptr; }
+            cudaFree(pp.orig); pp.orig = nullptr;
+        }
+        cudaFree(bin_key); cudaFree(bin_rank);
+        bin_key = bin_rank = nullptr;
+        pcap = 0;
+    }
+
+    int init() override {
+        const ink_params& p = P;
+        if (p.X <= 0 || p.Y <= 0 || p.Z <= 0) { err = "grid dims must be positive"; return 2; }
+        if ((long long)p.X * p.Y * p.Z >= (1ll << 32)) { err = "grid too large for 32-bit cell keys"; return 2; }
+        if (p.world_size != 1) { err = "multi-GPU contexts are created through ink_create with world_size > 1 (not built in this round)"; return 2; }
+        CK(cudaSetDevice(p.device));
+        cudaDeviceProp prop;
+        CK(cudaGetDeviceProperties(&prop, p.device));
+        if (prop.major < 10) { err = "libinkb200 is built for sm_100a (B200) only"; return 3; }
+        g.X = p.X; g.Y = p.Y; g.Z = p.Z;
+        g.sx = p.Z; g.sy = (long long)p.X * p.Z; g.n = (long long)p.X * p.Y * p.Z;
+        g.j0 = 0; g.j1 = p.Y;
+        // constants converted the way the reference's expressions convert them (float first, then Real)
+        C.h = (Real)p.cell_dim;
+        C.bx = (Real)(float)(p.X * p.cell_dim); C.by = (Real)(float)(p.Y * p.cell_dim); C.bz = (Real)(float)(p.Z * p.cell_dim);
+        C.rho = (Real)p.density; C.kvort = (Real)p.k_vort; C.visc = (Real)p.viscosity; C.patm = (Real)p.p_atm;
+        for (int a = 0; a < 3; ++a) C.g[a] = (Real)p.gravity[a];
+        C.lo = (Real)0.01f;
+        C.cx = (Real)(float)(p.X * p.cell_dim - 0.01f); C.cy = (Real)(float)(p.Y * p.cell_dim - 0.01f); C.cz = (Real)(float)(p.Z * p.cell_dim - 0.01f);
+        C.unit_h = (p.cell_dim == 1.0f);
+        C.R = p.buffer_size;
+        const size_t nb = (size_t)g.n * sizeof(Real);
+        for (auto& b : vel)
+            for (auto& ptr : b) { CK(cudaMalloc(&ptr, nb)); CK(cudaMemsetAsync(ptr, 0, nb, stream)); }
+        for (auto& ptr : curl) { CK(cudaMalloc(&ptr, nb)); CK(cudaMemsetAsync(ptr, 0, nb, stream)); }
+        for (Real** ptr : {&pres, &q, &rhs, &cg_r, &cg_d[0], &cg_d[1], &cg_w}) { CK(cudaMalloc(ptr, nb)); CK(cudaMemsetAsync(*ptr, 0, nb, stream)); }
+        CK(cudaMalloc(&S, sizeof(CgScal))); CK(cudaMemsetAsync(S, 0, sizeof(CgScal), stream));
+        CK(cudaMallocHost(&hS, sizeof(CgScal)));
+        CK(cudaMalloc(&seed, g.n)); CK(cudaMemsetAsync(seed, 0, g.n, stream));
+        CK(cudaMalloc(&mark, g.n)); CK(cudaMemsetAsync(mark, 0, g.n, stream));
+        CK(cudaMalloc(&d_scal, 4 * sizeof(unsigned int))); CK(cudaMemsetAsync(d_scal, 0, 4 * sizeof(unsigned int), stream));
+        CK(cudaMallocHost(&h_scal, 4 * sizeof(unsigned int)));
+        // counting-sort scratch: per-cell counts + scan levels
+        CK(cudaMalloc(&bin_count, (size_t)g.n * sizeof(uint32_t)));
+        long long m = g.n;
+        while (m > 1) {
+            m = (m + kScanTile - 1) / kScanTile;
+            uint32_t* lvl;
+            CK(cudaMalloc(&lvl, (size_t)std::max<long long>(m, 1) * sizeof(uint32_t)));
+            scan_lvl.push_back(lvl);
+            scan_n.push_back(m);
+        }
+        for (auto& e : ev) CK(cudaEventCreate(&e));
+        maxv_valid = true;  // zero field: max speed bits already 0
+        seed_valid = true;
+        CK(cudaStreamSynchronize(stream));
+        return 0;
+    }
+
+    // ---- helpers ---------------------------------------------------------------------------------
+    static bool is_device_ptr(const void* p) {
+        cudaPointerAttributes a;
+        if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+        return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+    }
+    int need_stage(size_t bytes) {
+        if (bytes <= stage_bytes) return 0;
+        if (stage) CK(cudaFree(stage));
+        stage = nullptr; stage_bytes = 0;
+        CK(cudaMalloc(&stage, bytes));
+        stage_bytes = bytes;
+        return 0;
+    }
+    // bring `bytes` of caller memory onto the device (no copy if it already is device memory)
+    int to_device(const void* src, size_t bytes, size_t stage_off, const void** out) {
+        if (is_device_ptr(src)) { *out = src; return 0; }
+        CK(cudaMemcpyAsync((char*)stage + stage_off, src, bytes, cudaMemcpyHostToDevice, stream));
+        *out = (char*)stage + stage_off;
+        return 0;
+    }
+    Real* U(int a) { return vel[cur][a]; }
+    Real* Un(int a) { return vel[cur ^ 1][a]; }
+    unsigned int cell_blocks() const { return nblk((long long)(g.j1 - g.j0) * g.sy); }
+    bool vec4() const { return (g.Z % 4) == 0; }
+    unsigned int cg_blocks() const {
+        const long long nvec = (long long)(g.j1 - g.j0) * g.X * (g.Z / (vec4() ? 4 : 1));
+        return (unsigned int)std::min<long long>(kCgMaxBlocks, std::max<long long>(1, (nvec + 255) / 256));
+    }
+
+    template <class T>
+    int grid_in(const void* src, Real* dst) {   // public (X,Y,Z) array of T -> internal
+        const void* d;
+        if (int rc = to_device(src, (size_t)g.n * sizeof(T), 0, &d)) return rc;
+        LAUNCH((k_xyz_to_internal<T, Real>), nblk(g.n), 256, g, (const T*)d, dst);
+        CK(cudaGetLastError());
+        if (d == stage) CK(cudaStreamSynchronize(stream));  // staging is reused by the next call
+        return 0;
+    }
+    template <class T>
+    int grid_out(const Real* src, void* dst) {
+        if (is_device_ptr(dst)) {
+            LAUNCH((k_internal_to_xyz<Real, T>), nblk(g.n), 256, g, src, (T*)dst);
+            CK(cudaGetLastError());
+            return 0;
+        }
+        LAUNCH((k_internal_to_xyz<Real, T>), nblk(g.n), 256, g, src, (T*)stage);
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(dst, stage, (size_t)g.n * sizeof(T), cudaMemcpyDeviceToHost, stream));
+        CK(cudaStreamSynchronize(stream));
+        return 0;
+    }
+    int grid_in_any(const void* src, Real* dst, int hd) {
+        if (int rc = need_stage((size_t)g.n * 8)) return rc;
+        return hd == 64 ? grid_in<double>(src, dst) : grid_in<float>(src, dst);
+    }
+    int grid_out_any(const Real* src, void* dst, int hd) {
+        if (int rc = need_stage((size_t)g.n * 8)) return rc;
+        return hd == 64 ? grid_out<double>(src, dst) : grid_out<float>(src, dst);
+    }
+    static int check_hd(int hd, std::string& err) {
+        if (hd != 32 && hd != 64) { err = "host_dtype must be 32 or 64"; return 2; }
+        return 0;
+    }
+
+    // ---- particles ---------------------------------------------------------------------------------
+    int reserve_particles(long long n) {
+        if (n <= pcap) return 0;
+        // keep existing content
+        Particles<Real> old[2] = {part[0], part[1]};
+        uint32_t *okey = bin_key, *orank = bin_rank;
+        const long long ncap = std::max<long long>(n, 1);
+        for (int b = 0; b < 2; ++b) {
+            for (int a = 0; a < 3; ++a) { CK(cudaMalloc(&part[b].p[a], (size_t)ncap * sizeof(Real))); CK(cudaMalloc(&part[b].v[a], (size_t)ncap * sizeof(Real))); }
+            CK(cudaMalloc(&part[b].orig, (size_t)ncap * sizeof(uint32_t)));
+        }
+        CK(cudaMalloc(&bin_key, (size_t)ncap * sizeof(uint32_t)));
+        CK(cudaMalloc(&bin_rank, (size_t)ncap * sizeof(uint32_t)));
+        if (np > 0) {
+            for (int a = 0; a < 3; ++a) {
+                CK(cudaMemcpyAsync(part[pcur].p[a], old[pcur].p[a], (size_t)np * sizeof(Real), cudaMemcpyDeviceToDevice, stream));
+                CK(cudaMemcpyAsync(part[pcur].v[a], old[pcur].v[a], (size_t)np * sizeof(Real), cudaMemcpyDeviceToDevice, stream));
+            }
+            CK(cudaMemcpyAsync(part[pcur].orig, old[pcur].orig, (size_t)np * sizeof(uint32_t), cudaMemcpyDeviceToDevice, stream));
+        }
+        CK(cudaStreamSynchronize(stream));
+        for (auto& o : old) {
+            for (auto& p : o.p) cudaFree(p);
+            for (auto& p : o.v) cudaFree(p);
+            cudaFree(o.orig);
+        }
+        cudaFree(okey); cudaFree(orank);
+        pcap = ncap;
+        return 0;
+    }
+
+    // particles are stored in caller order first (orig = identity over the concatenated drops), then binned
+    int set_particles(int drop, const void* pos, const void* vel_, int64_t n, int hd) override {
+        if (int rc = check_hd(hd, err)) return rc;
+        if (drop < 0 || n < 0) { err = "bad drop / n"; return 2; }
+        if (drop > (int)drop_n.size()) { err = "drops must be added in order (0, 1, ...)"; return 2; }
+        // rebuild the concatenation in caller order: un-bin what we have, replace / append this drop
+        std::vector<long long> new_n = drop_n;
+        if (drop == (int)new_n.size()) new_n.push_back(n); else new_n[drop] = n;
+        std::vector<long long> new_off(new_n.size());
+        long long tot = 0;
+        for (size_t d = 0; d < new_n.size(); ++d) { new_off[d] = tot; tot += new_n[d]; }
+        if (tot >= (1ll << 32)) { err = "more than 2^32-1 particles on one device"; return 2; }
+        const size_t es = hd == 64 ? 8 : 4;
+        // 1) export the other drops (caller order) into a temporary AoS snapshot in Real
+        std::vector<Real*> keep_pos(drop_n.size(), nullptr), keep_vel(drop_n.size(), nullptr);
+        for (size_t d = 0; d < drop_n.size(); ++d) {
+            if ((int)d == drop || drop_n[d] == 0) continue;
+            CK(cudaMalloc(&keep_pos[d], (size_t)drop_n[d] * 3 * sizeof(Real)));
+            CK(cudaMalloc(&keep_vel[d], (size_t)drop_n[d] * 3 * sizeof(Real)));
+            LAUNCH((k_export_aos<Real, Real>), nblk(np), 256, np, drop_off[d], drop_n[d], part[pcur], keep_pos[d], keep_vel[d]);
+        }
+        CK(cudaGetLastError());
+        const long long old_np = np;
+        np = 0;  // content is rebuilt below; do not copy in reserve
+        if (int rc = reserve_particles(tot)) { np = old_np; return rc; }
+        for (size_t d = 0; d < new_n.size(); ++d) {
+            if (new_n[d] == 0) continue;
+            if ((int)d == drop) {
+                if (int rc = need_stage((size_t)n * 3 * es * 2)) return rc;
+                const void *dp, *dv = nullptr;
+                if (int rc = to_device(pos, (size_t)n * 3 * es, 0, &dp)) return rc;
+                if (vel_) if (int rc = to_device(vel_, (size_t)n * 3 * es, (size_t)n * 3 * es, &dv)) return rc;
+                if (hd == 64) LAUNCH((k_import_aos<double, Real>), nblk(n), 256, n, new_off[d], (const double*)dp, (const double*)dv, part[pcur]);
+                else LAUNCH((k_import_aos<float, Real>), nblk(n), 256, n, new_off[d], (const float*)dp, (const float*)dv, part[pcur]);
+            } else {
+                LAUNCH((k_import_aos<Real, Real>), nblk(new_n[d]), 256, new_n[d], new_off[d], (const Real*)keep_pos[d], (const Real*)keep_vel[d], part[pcur]);
+            }
+        }
+        CK(cudaGetLastError());
+        CK(cudaStreamSynchronize(stream));
+        for (auto p : keep_pos) cudaFree(p);
+        for (auto p : keep_vel) cudaFree(p);
+        drop_n = new_n; drop_off = new_off; np = tot;
+        seed_valid = false;
+        return resort();
+    }
+    int num_drops() const override { return (int)drop_n.size(); }
+    int64_t num_particles(int drop) const override { return (drop >= 0 && drop < (int)drop_n.size()) ? drop_n[drop] : 0; }
+
+    int get_particles(int drop, void* pos, void* vel_, int hd) override {
+        if (int rc = check_hd(hd, err)) return rc;
+        if (drop < 0 || drop >= (int)drop_n.size()) { err = "no such drop"; return 2; }
+        const long long n = drop_n[drop];
+        if (n == 0) return 0;
+        const size_t es = hd == 64 ? 8 : 4, bytes = (size_t)n * 3 * es;
+        const bool dpos = pos && is_device_ptr(pos), dvel = vel_ && is_device_ptr(vel_);
+        if (int rc = need_stage(bytes * 2)) return rc;
+        void* op = pos ? (dpos ? pos : stage) : nullptr;
+        void* ov = vel_ ? (dvel ? vel_ : (char*)stage + bytes) : nullptr;
+        if (hd == 64) LAUNCH((k_export_aos<Real, double>), nblk(np), 256, np, drop_off[drop], n, part[pcur], (double*)op, (double*)ov);
+        else LAUNCH((k_export_aos<Real, float>), nblk(np), 256, np, drop_off[drop], n, part[pcur], (float*)op, (float*)ov);
+        CK(cudaGetLastError());
+        if (pos && !dpos) CK(cudaMemcpyAsync(pos, op, bytes, cudaMemcpyDeviceToHost, stream));
+        if (vel_ && !dvel) CK(cudaMemcpyAsync(vel_, ov, bytes, cudaMemcpyDeviceToHost, stream));
+        CK(cudaStreamSynchronize(stream));
+        return 0;
+    }
+
+    int scan_counts() {   // exclusive scan of bin_count in place
+        long long m = g.n;
+        uint32_t* in = bin_count;
+        size_t lvl = 0;
+        std::vector<uint32_t*> ins;
+        std::vector<long long> ns;
+        while (true) {
+            const long long tiles = (m + kScanTile - 1) / kScanTile;
+            LAUNCH(k_scan_tiles, (unsigned int)tiles, 256, m, in, in, scan_lvl[lvl]);
+            ins.push_back(in); ns.push_back(m);
+            if (tiles == 1) break;
+            in = scan_lvl[lvl]; m = tiles; ++lvl;
+        }
+        for (int l = (int)ins.size() - 2; l >= 0; --l) LAUNCH(k_scan_add, nblk(ns[l]), 256, ns[l], ins[l], ins[l + 1]);
+        CK(cudaGetLastError());
+        return 0;
+    }
+    int resort() override {
+        since_sort = 0;
+        if (np == 0) return 0;
+        CK(cudaMemsetAsync(bin_count, 0, (size_t)g.n * sizeof(uint32_t), stream));
+        LAUNCH((k_bin_count<Real>), nblk(np), 256, g, np, part[pcur], bin_count, bin_key, bin_rank);
+        if (int rc = scan_counts()) return rc;
+        LAUNCH((k_bin_scatter<Real>), nblk(np), 256, np, part[pcur], part[pcur ^ 1], bin_count, bin_key, bin_rank);
+        CK(cudaGetLastError());
+        pcur ^= 1;
+        ++stats.resorts;
+        return 0;
+    }
+    int ensure_seed() {
+        if (seed_valid) return 0;
+        CK(cudaMemsetAsync(seed, 0, g.n, stream));
+        CK(cudaMemsetAsync(d_scal + 1, 0, sizeof(unsigned int), stream));
+        if (np > 0) LAUNCH((k_mark_particle_cells<Real>), nblk(np), 256, g, np, part[pcur], seed, d_scal + 1);
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(h_scal + 1, d_scal + 1, sizeof(unsigned int), cudaMemcpyDeviceToHost, stream));
+        CK(cudaStreamSynchronize(stream));
+        oob_now = h_scal[1] > 0;
+        if (oob_now) have_phantom = true;
+        seed_valid = true;
+        return 0;
+    }
+
+    // ---- grid state --------------------------------------------------------------------------------
+    int set_velocity(const void* u, const void* v, const void* w, int hd) override {
+        if (int rc = check_hd(hd, err)) return rc;
+        const void* src[3] = {u, v, w};
+        for (int a = 0; a < 3; ++a)
+            if (int rc = grid_in_any(src[a], U(a), hd)) return rc;
+        maxv_valid = false;
+        return 0;
+    }
+    int get_field(int which, void* u, void* v, void* w, int hd) override {
+        if (int rc = check_hd(hd, err)) return rc;
+        void* dst[3] = {u, v, w};
+        for (int a = 0; a < 3; ++a) {
+            if (!dst[a]) continue;
+            const Real* src = (which == INK_FIELD_CURL) ? curl[a] : U(a);   // old == curr between phases
+            if (int rc = grid_out_any(src, dst[a], hd)) return rc;
+        }
+        return 0;
+    }
+    int get_pressure(void* p, int hd) override {
+        if (int rc = check_hd(hd, err)) return rc;
+        return grid_out_any(pres, p, hd);
+    }
+    int set_pressure(const void* p, int hd) override {
+        if (int rc = check_hd(hd, err)) return rc;
+        if (int rc = grid_in_any(p, pres, hd)) return rc;
+        LAUNCH((k_add_scalar<Real>), nblk(g.n), 256, g.n, -C.patm, pres, q);
+        CK(cudaGetLastError());
+        have_q = true;
+        return 0;
+    }
+    int get_mark(uint8_t* m) override {
+        if (int rc = need_stage((size_t)g.n * 8)) return rc;
+        uint8_t* dst = is_device_ptr(m) ? m : (uint8_t*)stage;
+        LAUNCH(k_mark_to_xyz, nblk(g.n), 256, g, mark, dst);
+        CK(cudaGetLastError());
+        if (dst != m) CK(cudaMemcpyAsync(m, dst, g.n, cudaMemcpyDeviceToHost, stream));
+        CK(cudaStreamSynchronize(stream));
+        return 0;
+    }
+    int get_divergence(void* d, int hd) override {
+        if (int rc = check_hd(hd, err)) return rc;
+        LAUNCH((k_divergence<Real>), cell_blocks(), 256, g, 0, Real(0), Real(0), U(0), U(1), U(2), rhs);
+        CK(cudaGetLastError());
+        return grid_out_any(rhs, d, hd);
+    }
+    int sample_velocity(const void* pos, int64_t n, void* out, int hd) override {
+        if (int rc = check_hd(hd, err)) return rc;
+        if (n <= 0) return 0;
+        const size_t es = hd == 64 ? 8 : 4;
+        // stage: [host copy in | Real in | Real out | host out]
+        const size_t a0 = (size_t)n * 3 * es, a1 = (size_t)n * 3 * sizeof(Real);
+        if (int rc = need_stage(2 * a0 + 2 * a1)) return rc;
+        const void* dp;
+        if (int rc = to_device(pos, a0, 0, &dp)) return rc;
+        Real* rin = (Real*)((char*)stage + a0);
+        Real* rout = (Real*)((char*)stage + a0 + a1);
+        void* hout = (char*)stage + a0 + 2 * a1;
+        // reuse the generic converters through a flat "grid" of n*3 elements
+        if (hd == 64) LAUNCH((k_convert<double, Real>), nblk(n * 3), 256, n * 3, (const double*)dp, rin);
+        else LAUNCH((k_convert<float, Real>), nblk(n * 3), 256, n * 3, (const float*)dp, rin);
+        if (P.arith == INK_ARITH_FAST) LAUNCH((k_sample<Real, true>), nblk(n), 256, g, C, (long long)n, rin, rout, U(0), U(1), U(2));
+        else LAUNCH((k_sample<Real, false>), nblk(n), 256, g, C, (long long)n, rin, rout, U(0), U(1), U(2));
+        const bool dout = is_device_ptr(out);
+        void* o = dout ? out : hout;
+        if (hd == 64) LAUNCH((k_convert<Real, double>), nblk(n * 3), 256, n * 3, rout, (double*)o);
+        else LAUNCH((k_convert<Real, float>), nblk(n * 3), 256, n * 3, rout, (float*)o);
+        CK(cudaGetLastError());
+        if (!dout) CK(cudaMemcpyAsync(out, o, a0, cudaMemcpyDeviceToHost, stream));
+        CK(cudaStreamSynchronize(stream));
+        return 0;
+    }
+
+    // ---- phases --------------------------------------------------------------------------------------
+    int read_max_speed(float* out) {
+        if (!maxv_valid) {
+            CK(cudaMemsetAsync(d_scal, 0, sizeof(unsigned int), stream));
+            const unsigned int b = std::min<unsigned int>(cell_blocks(), kSMs * 8);
+            LAUNCH((k_max_speed<Real>), b, 256, g, U(0), U(1), U(2), d_scal);
+            CK(cudaGetLastError());
+            maxv_valid = true;
+        }
+        CK(cudaMemcpyAsync(h_scal, d_scal, sizeof(unsigned int), cudaMemcpyDeviceToHost, stream));
+        CK(cudaStreamSynchronize(stream));
+        float m;
+        memcpy(&m, h_scal, 4);
+        *out = m;
+        return 0;
+    }
+    float last_grid_maxv = 0.f;
+    // System::calcTimeStep (src/waterSolver.cpp:13-38; Q12) — the scalar logic runs on the host in the reference's float arithmetic
+    int calc_dt(double ttnr, double* dt_out) override {
+        float maxVelocity = 0.f;
+        if (int rc = read_max_speed(&maxVelocity)) return rc;
+        last_grid_maxv = maxVelocity;
+        if (have_phantom) {  // phantom map cells of out-of-grid particles also enter the maximum (Q8)
+            const float s = (float)std::sqrt(phantom_v[0] * phantom_v[0] + (phantom_v[1] * phantom_v[1] + phantom_v[2] * phantom_v[2]));
+            if (maxVelocity < s) maxVelocity = s;
+        }
+        double dt;
+        if (std::isinf(maxVelocity) || maxVelocity == 0.f) dt = P.dt_min;
+        else {
+            float timeStep = P.k_cfl * (P.cell_dim / maxVelocity);
+            timeStep = std::max(std::min(timeStep, P.dt_max), P.dt_min);
+            // the reference assigns the min to its FLOAT local (src/waterSolver.cpp:35): narrowed even when ttnr wins
+            timeStep = (float)std::min(ttnr, (double)timeStep);
+            dt = timeStep;
+        }
+        stats.dt = dt;
+        if (dt_out) *dt_out = dt;
+        return 0;
+    }
+    void swap_vel() { cur ^= 1; }
+
+    int advect_impl(Real dt, bool allow_skip) {
+        stats.advect_skipped = 0;
+        if (allow_skip) {
+            // With CFL-limited dt the back-traced cell centre cannot leave its cell, so the nearest-cell copy is the
+            // identity: every sampled component is a convex combination of grid values, |v_c| <= max|v|.
+            float mv;
+            if (int rc = read_max_speed(&mv)) return rc;
+            const double h = P.cell_dim, margin = std::min(0.5 * h, 1.0 - 0.5 * h);
+            if (margin > 0 && std::isfinite(mv) && std::fabs((double)dt) * (double)mv <= 0.9 * margin) { stats.advect_skipped = 1; return 0; }
+        }
+        LAUNCH((k_advect<Real>), cell_blocks(), 256, g, C, dt, U(0), U(1), U(2), Un(0), Un(1), Un(2));
+        CK(cudaGetLastError());
+        swap_vel();
+        maxv_valid = false;
+        return 0;
+    }
+    int advect(double dt) override { return advect_impl((Real)(float)dt, true); }
+
+    int forces_impl(Real dt) {
+        if (int rc = ensure_seed()) return rc;
+        const Real gx = dt * C.g[0], gy = dt * C.g[1], gz = dt * C.g[2];
+        LAUNCH((k_dilate_add_gravity<Real>), cell_blocks(), 256, g, C.R, seed, mark, gx, gy, gz, U(0), U(1), U(2));
+        CK(cudaGetLastError());
+        if (oob_now) { phantom_v[0] += gx; phantom_v[1] += gy; phantom_v[2] += gz; }
+        maxv_valid = false;
+        return 0;
+    }
+    int forces(double dt) override { return forces_impl((Real)(float)dt); }
+
+    int viscosity_impl(Real dt) {
+        const Real s = dt * C.visc;
+        LAUNCH((k_viscosity<Real>), cell_blocks(), 256, g, s, U(0), U(1), U(2), Un(0), Un(1), Un(2));
+        CK(cudaGetLastError());
+        swap_vel();
+        maxv_valid = false;
+        return 0;
+    }
+    int viscosity(double dt) override { return viscosity_impl((Real)(float)dt); }
+
+    int pressure_rhs(double dt_, void* b, int hd) override {
+        if (int rc = check_hd(hd, err)) return rc;
+        const Real dt = (Real)(float)dt_;
+        const Real scale = (C.rho * C.h) / dt;
+        LAUNCH((k_divergence<Real>), cell_blocks(), 256, g, 1, scale, C.patm, U(0), U(1), U(2), rhs);
+        CK(cudaGetLastError());
+        return grid_out_any(rhs, b, hd);
+    }
+
+    // solve M x = f (M = -A) by CG; x holds the initial guess
+    int cg_solve(const Real* f, Real* x) {
+        const unsigned int nb = cg_blocks();
+        const double tol2 = P.cg_rtol * P.cg_rtol;
+        CK(cudaMemcpyAsync(&S->tol2, &tol2, sizeof(double), cudaMemcpyHostToDevice, stream));
+        if (vec4()) LAUNCH((k_cg_init<Real, 4>), nb, 256, g, S, f, x, cg_r);
+        else LAUNCH((k_cg_init<Real, 1>), nb, 256, g, S, f, x, cg_r);
+        CK(cudaGetLastError());
+        const size_t head = offsetof(CgScal, partial);
+        CK(cudaMemcpyAsync(hS, S, head, cudaMemcpyDeviceToHost, stream));
+        CK(cudaStreamSynchronize(stream));
+        if (hS->bb == 0.0) {  // f == 0: the solution is exactly 0
+            CK(cudaMemsetAsync(x, 0, (size_t)g.n * sizeof(Real), stream));
+            stats.cg_iters = 0; stats.cg_rel_residual = 0;
+            return 0;
+        }
+        int dcur = 0, launched = 0;
+        const int every = std::max(1, P.cg_check_every);
+        while (!hS->done && launched < P.cg_max_iters) {
+            const int batch = std::min(every, P.cg_max_iters - launched);
+            for (int it = 0; it < batch; ++it) {
+                if (vec4()) {
+                    LAUNCH((k_cg_dir_matvec<Real, 4>), nb, 256, g, S, cg_r, cg_d[dcur], cg_d[dcur ^ 1], cg_w);
+                    LAUNCH((k_cg_update<Real, 4>), nb, 256, g, S, x, cg_r, cg_d[dcur ^ 1], cg_w);
+                } else {
+                    LAUNCH((k_cg_dir_matvec<Real, 1>), nb, 256, g, S, cg_r, cg_d[dcur], cg_d[dcur ^ 1], cg_w);
+                    LAUNCH((k_cg_update<Real, 1>), nb, 256, g, S, x, cg_r, cg_d[dcur ^ 1], cg_w);
+                }
+                dcur ^= 1;
+            }
+            launched += batch;
+            CK(cudaGetLastError());
+            CK(cudaMemcpyAsync(hS, S, head, cudaMemcpyDeviceToHost, stream));
+            CK(cudaStreamSynchronize(stream));
+        }
+        stats.cg_iters = hS->iters;
+        stats.cg_rel_residual = std::sqrt(hS->rr / hS->bb);
+        return 0;
+    }
+
+    int grad_subtract(Real dt) {
+        const Real s = dt / (C.rho * C.h);
+        LAUNCH((k_grad_subtract<Real>), cell_blocks(), 256, g, s, pres, U(0), U(1), U(2));
+        CK(cudaGetLastError());
+        maxv_valid = false;
+        return 0;
+    }
+    int pressure_impl(Real dt) {
+        const Real scale = (C.rho * C.h) / dt;
+        LAUNCH((k_divergence<Real>), cell_blocks(), 256, g, 2, scale, C.patm, U(0), U(1), U(2), rhs);
+        CK(cudaGetLastError());
+        if (!(P.cg_warm_start && have_q)) CK(cudaMemsetAsync(q, 0, (size_t)g.n * sizeof(Real), stream));
+        if (int rc = cg_solve(rhs, q)) return rc;
+        have_q = true;
+        LAUNCH((k_add_scalar<Real>), nblk(g.n), 256, g.n, C.patm, q, pres);
+        CK(cudaGetLastError());
+        return grad_subtract(dt);
+    }
+    int pressure(double dt) override { return pressure_impl((Real)(float)dt); }
+    int pressure_given_p(double dt) override { return grad_subtract((Real)(float)dt); }
+
+    int poisson_solve(const void* b, void* p, int hd) override {
+        if (int rc = check_hd(hd, err)) return rc;
+        if (int rc = grid_in_any(b, rhs, hd)) return rc;
+        LAUNCH((k_scale<Real>), nblk(g.n), 256, g.n, Real(-1), rhs);
+        CK(cudaMemsetAsync(cg_d[0], 0, (size_t)g.n * sizeof(Real), stream));
+        Real* x = curl[0];   // scratch: curl is rewritten by the next vorticity phase before use
+        CK(cudaMemsetAsync(x, 0, (size_t)g.n * sizeof(Real), stream));
+        if (int rc = cg_solve(rhs, x)) return rc;
+        return grid_out_any(x, p, hd);
+    }
+
+    int vorticity_impl(Real dt) {
+        LAUNCH((k_curl<Real>), cell_blocks(), 256, g, U(0), U(1), U(2), curl[0], curl[1], curl[2]);
+        CK(cudaMemsetAsync(d_scal, 0, sizeof(unsigned int), stream));
+        LAUNCH((k_vorticity<Real>), cell_blocks(), 256, g, dt, C.kvort, curl[0], curl[1], curl[2], U(0), U(1), U(2), d_scal);
+        CK(cudaGetLastError());
+        maxv_valid = true;   // fused K0
+        return 0;
+    }
+    int vorticity(double dt) override { return vorticity_impl((Real)(float)dt); }
+
+    int velocity_field_update(double dt_) override {
+        const Real dt = (Real)(float)dt_;
+        if (int rc = advect_impl(dt, true)) return rc;
+        if (int rc = forces_impl(dt)) return rc;
+        if (int rc = viscosity_impl(dt)) return rc;
+        if (int rc = pressure_impl(dt)) return rc;
+        return vorticity_impl(dt);
+    }
+
+    int particles_impl(Real dt) {
+        if (np == 0) return 0;
+        CK(cudaMemsetAsync(seed, 0, g.n, stream));
+        if (P.arith == INK_ARITH_FAST) LAUNCH((k_particles_rk2<Real, true>), nblk(np), 256, g, C, dt, np, part[pcur], U(0), U(1), U(2), seed);
+        else LAUNCH((k_particles_rk2<Real, false>), nblk(np), 256, g, C, dt, np, part[pcur], U(0), U(1), U(2), seed);
+        CK(cudaGetLastError());
+        // K8 seeded the mask from the new positions, and the wall clamp put every particle inside the grid; phantom
+        // cells created earlier persist in the reference's map (their velocity keeps entering calcTimeStep)
+        seed_valid = true;
+        oob_now = false;
+        ++since_sort;
+        return 0;
+    }
+    int particles(double dt) override {
+        if (int rc = particles_impl((Real)(float)dt)) return rc;
+        if (P.resort_interval > 0 && since_sort >= P.resort_interval) return resort();
+        return 0;
+    }
+
+    // System::solve (src/inkSolver.cpp:5-9)
+    int step(double ttnr, double* dt_out) override {
+        double dt_;
+        CK(cudaEventRecord(ev[0], stream));
+        if (int rc = calc_dt(ttnr, &dt_)) return rc;
+        const Real dt = (Real)(float)dt_;   // `float timeStep` parameters narrow the double (Q15)
+        CK(cudaEventRecord(ev[1], stream));
+        if (int rc = advect_impl(dt, true)) return rc;
+        CK(cudaEventRecord(ev[2], stream));
+        if (int rc = forces_impl(dt)) return rc;
+        CK(cudaEventRecord(ev[3], stream));
+        if (int rc = viscosity_impl(dt)) return rc;
+        CK(cudaEventRecord(ev[4], stream));
+        if (int rc = pressure_impl(dt)) return rc;
+        CK(cudaEventRecord(ev[5], stream));
+        if (int rc = vorticity_impl(dt)) return rc;
+        CK(cudaEventRecord(ev[6], stream));
+        if (int rc = particles_impl(dt)) return rc;
+        CK(cudaEventRecord(ev[7], stream));
+        if (P.resort_interval > 0 && since_sort >= P.resort_interval)
+            if (int rc = resort()) return rc;
+        CK(cudaEventRecord(ev[8], stream));
+        ev_valid = true;
+        ++stats.steps;
+        if (dt_out) *dt_out = dt_;
+        return 0;
+    }
+    int phase_ms(float out[8]) override {
+        if (!ev_valid) { err = "no ink_step yet"; return 2; }
+        CK(cudaEventSynchronize(ev[8]));
+        for (int a = 0; a < 8; ++a) CK(cudaEventElapsedTime(&out[a], ev[a], ev[a + 1]));
+        return 0;
+    }
+};
+
+}  // namespace ink
+
+// -------------------------------------------------------------------------------------------------
+using namespace ink;
+struct ink_ctx { CtxBase* impl; };
+
+extern "C" {
+
+void ink_default_params(ink_params* p) {
+    memset(p, 0, sizeof *p);
+    p->X = 20; p->Y = 45; p->Z = 20;           // src/system.h:15-17
+    p->cell_dim = 1.f; p->density = .95f; p->k_vort = 1.f; p->viscosity = 1.0016f; p->p_atm = 1.f;
+    p->gravity[0] = 0.f; p->gravity[1] = -0.1f; p->gravity[2] = 0.f;
+    p->k_cfl = 0.2f; p->dt_min = 0.005f; p->dt_max = 1.f; p->buffer_size = 3;
+    p->precision = 32; p->arith = INK_ARITH_STRICT; p->device = 0;
+    p->cg_rtol = 1e-6; p->cg_max_iters = 20000; p->cg_check_every = 16; p->cg_warm_start = 1; p->cg_precond = INK_PCG_NONE;
+    p->resort_interval = 16;
+    p->rank = 0; p->world_size = 1;
+}
+
+int ink_nccl_unique_id(uint8_t out[128]) { memset(out, 0, 128); return 0; }
+
+int ink_create(const ink_params* p, ink_ctx** out) {
+    if (!p || !out) return 2;
+    *out = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        g_create_error = "no CUDA device: libinkb200 has no CPU fallback";
+        return 3;
+    }
+    CtxBase* c;
+    if (p->precision == 32) c = new Ctx<float>();
+    else if (p->precision == 64) c = new Ctx<double>();
+    else { g_create_error = "precision must be 32 or 64"; return 2; }
+    c->P = *p;
+    if (c->P.precision == 32 && c->P.cg_rtol < 1e-7) c->P.cg_rtol = 1e-7;
+    int rc = c->init();
+    if (rc) { g_create_error = c->err; delete c; return rc; }
+    *out = new ink_ctx{c};
+    return 0;
+}
+void ink_destroy(ink_ctx* c) {
+    if (!c) return;
+    delete c->impl;
+    delete c;
+}
+const char* ink_last_error(const ink_ctx* c) { return c ? c->impl->err.c_str() : g_create_error.c_str(); }
+int ink_sync(ink_ctx* c) { return cudaStreamSynchronize(c->impl->stream) == cudaSuccess ? 0 : 1; }
+
+int ink_set_particles(ink_ctx* c, int drop, const void* pos, const void* vel, int64_t n, int hd) { return c->impl->set_particles(drop, pos, vel, n, hd); }
+int ink_num_drops(const ink_ctx* c) { return c->impl->num_drops(); }
+int64_t ink_num_particles(const ink_ctx* c, int drop) { return c->impl->num_particles(drop); }
+int ink_get_particles(ink_ctx* c, int drop, void* pos, void* vel, int hd) { return c->impl->get_particles(drop, pos, vel, hd); }
+int ink_set_velocity(ink_ctx* c, const void* u, const void* v, const void* w, int hd) { return c->impl->set_velocity(u, v, w, hd); }
+int ink_get_field(ink_ctx* c, int which, void* u, void* v, void* w, int hd) { return c->impl->get_field(which, u, v, w, hd); }
+int ink_get_pressure(ink_ctx* c, void* p, int hd) { return c->impl->get_pressure(p, hd); }
+int ink_set_pressure(ink_ctx* c, const void* p, int hd) { return c->impl->set_pressure(p, hd); }
+int ink_get_mark(ink_ctx* c, uint8_t* m) { return c->impl->get_mark(m); }
+int ink_get_divergence(ink_ctx* c, void* d, int hd) { return c->impl->get_divergence(d, hd); }
+int ink_sample_velocity(ink_ctx* c, const void* pos, int64_t n, void* out, int hd) { return c->impl->sample_velocity(pos, n, out, hd); }
+
+int ink_step(ink_ctx* c, double ttnr, double* dt_out) { return c->impl->step(ttnr, dt_out); }
+int ink_calc_dt(ink_ctx* c, double ttnr, double* dt_out) { return c->impl->calc_dt(ttnr, dt_out); }
+int ink_advect(ink_ctx* c, double dt) { return c->impl->advect(dt); }
+int ink_forces(ink_ctx* c, double dt) { return c->impl->forces(dt); }
+int ink_viscosity(ink_ctx* c, double dt) { return c->impl->viscosity(dt); }
+int ink_pressure_rhs(ink_ctx* c, double dt, void* b, int hd) { return c->impl->pressure_rhs(dt, b, hd); }
+int ink_pressure(ink_ctx* c, double dt) { return c->impl->pressure(dt); }
+int ink_pressure_given_p(ink_ctx* c, double dt) { return c->impl->pressure_given_p(dt); }
+int ink_poisson_solve(ink_ctx* c, const void* b, void* p, int hd) { return c->impl->poisson_solve(b, p, hd); }
+int ink_vorticity(ink_ctx* c, double dt) { return c->impl->vorticity(dt); }
+int ink_velocity_field_update(ink_ctx* c, double dt) { return c->impl->velocity_field_update(dt); }
+int ink_particles(ink_ctx* c, double dt) { return c->impl->particles(dt); }
+int ink_resort_particles(ink_ctx* c) { return c->impl->resort(); }
+
+int ink_get_stats(ink_ctx* c, ink_stats* out) { *out = c->impl->stats; return 0; }
+int ink_get_phase_ms(ink_ctx* c, float out[8]) { return c->impl->phase_ms(out); }
+
+}  // extern "C"

@@ -1,0 +1,222 @@
+// cg.cuh — matrix-free conjugate-gradient solve of the pressure-Poisson system, replacing the reference's
+// pre-factored Eigen::SparseLU (src/system.h:105; assembly src/waterSolver.cpp:240-261; solve :279).
+//
+// The reference matrix A has diag -6 in every row and +1 per in-grid neighbour (ghost pressure on all six faces
+// moved to the RHS, Q10).  We solve the SPD system  M x = f,  M = -A  (M x)_c = 6 x_c - sum_{in-grid nbrs} x_n.
+//
+// One CG iteration = 2 kernels, 40 B/cell in fp32 (80 in fp64):
+//   k_cg_dir_matvec : d' = r + beta d  (recomputed at the 6 neighbours from r,d instead of a third pass),
+//                     w = M d', partial <d', w>            reads r,d  writes d',w   (16 B)
+//   k_cg_update     : x += alpha d', r -= alpha w, partial <r, r>  reads x,d',r,w writes x,r (24 B)
+// alpha/beta live in device memory (no host round trip); dot products accumulate in fp64 and are reduced
+// warp-shuffle -> block -> fixed-order last-block pass (deterministic, no float atomics).
+// Each thread owns V=4 consecutive z cells (128-bit loads/stores) when Z % 4 == 0.
+#pragma once
+#include "common.cuh"
+
+namespace ink {
+
+constexpr int kCgMaxBlocks = 148 * 8;
+
+struct CgScal {
+    double rr, rr_old, dw, bb, tol2;
+    int iters, done;
+    unsigned int ticket;
+    int pad;
+    double partial[2][kCgMaxBlocks];
+};
+
+template <class Real, int V>
+struct alignas(sizeof(Real) * V) Pack { Real a[V]; };
+
+template <class Real, int V>
+__device__ __forceinline__ Pack<Real, V> ldp(const Real* p) { return *reinterpret_cast<const Pack<Real, V>*>(p); }
+template <class Real, int V>
+__device__ __forceinline__ void stp(Real* p, const Pack<Real, V>& v) { *reinterpret_cast<Pack<Real, V>*>(p) = v; }
+
+// block-level fp64 sum -> S->partial[slot][block]; the last block to arrive adds all partials in a fixed order
+// and returns true (thread 0 of that block holds the total in `total`).
+__device__ __forceinline__ bool block_sum_last(double acc, CgScal* S, int slot, double& total) {
+    __shared__ double ssum[8];
+    __shared__ bool is_last;
+    acc = warp_sum(acc);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (lane == 0) ssum[wid] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double b = 0;
+        for (int q = 0; q < (int)(blockDim.x >> 5); ++q) b += ssum[q];
+        S->partial[slot][blockIdx.x] = b;
+        __threadfence();
+        const unsigned int t = atomicAdd(&S->ticket, 1u);
+        is_last = (t == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!is_last) return false;
+    __threadfence();
+    if (wid == 0) {
+        double s = 0;
+        for (int q = lane; q < (int)gridDim.x; q += 32) s += __ldcg(&S->partial[slot][q]);
+        s = warp_sum(s);
+        total = s;
+        if (lane == 0) S->ticket = 0;
+    }
+    return true;
+}
+
+template <class Real, int V>
+__device__ __forceinline__ void vec_cell(const Grid& g, long long t, int ZV, int& i, int& j, int& k, long long& c) {
+    const int kv = (int)(t % ZV);
+    const long long row = t / ZV;
+    i = (int)(row % g.X);
+    j = g.j0 + (int)(row / g.X);
+    k = kv * V;
+    c = (long long)j * g.sy + (long long)i * g.sx + k;
+}
+
+// r = f - M x, <r,r>, <f,f>;  (x may be a warm start)
+template <class Real, int V>
+__global__ void __launch_bounds__(256) k_cg_init(Grid g, CgScal* S, const Real* __restrict__ f, const Real* __restrict__ x, Real* __restrict__ r) {
+    const int ZV = g.Z / V;
+    const long long nvec = (long long)(g.j1 - g.j0) * g.X * ZV;
+    double arr = 0, abb = 0;
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < nvec; t += (long long)gridDim.x * blockDim.x) {
+        int i, j, k; long long c;
+        vec_cell<Real, V>(g, t, ZV, i, j, k, c);
+        const Pack<Real, V> xc = ldp<Real, V>(x + c), fc = ldp<Real, V>(f + c);
+        Real sum[V];
+#pragma unroll
+        for (int a = 0; a < V; ++a) sum[a] = Real(0);
+        if (i + 1 < g.X) { const Pack<Real, V> q = ldp<Real, V>(x + c + g.sx);
+#pragma unroll
+            for (int a = 0; a < V; ++a) sum[a] += q.a[a]; }
+        if (i - 1 >= 0) { const Pack<Real, V> q = ldp<Real, V>(x + c - g.sx);
+#pragma unroll
+            for (int a = 0; a < V; ++a) sum[a] += q.a[a]; }
+        if (j + 1 < g.Y) { const Pack<Real, V> q = ldp<Real, V>(x + c + g.sy);
+#pragma unroll
+            for (int a = 0; a < V; ++a) sum[a] += q.a[a]; }
+        if (j - 1 >= 0) { const Pack<Real, V> q = ldp<Real, V>(x + c - g.sy);
+#pragma unroll
+            for (int a = 0; a < V; ++a) sum[a] += q.a[a]; }
+        const Real zl = (k > 0) ? x[c - 1] : Real(0);
+        const Real zr = (k + V < g.Z) ? x[c + V] : Real(0);
+        Pack<Real, V> rc;
+#pragma unroll
+        for (int a = 0; a < V; ++a) {
+            const Real left = (a > 0) ? xc.a[a > 0 ? a - 1 : 0] : zl;
+            const Real right = (a < V - 1) ? xc.a[a < V - 1 ? a + 1 : 0] : zr;
+            const Real mx = Real(6) * xc.a[a] - (sum[a] + left + right);
+            rc.a[a] = fc.a[a] - mx;
+            arr += (double)rc.a[a] * (double)rc.a[a];
+            abb += (double)fc.a[a] * (double)fc.a[a];
+        }
+        stp<Real, V>(r + c, rc);
+    }
+    double tot_rr, tot_bb = 0;
+    // two reductions through the same ticket: do <f,f> first via slot 1 without the ticket (plain partials)
+    {
+        __shared__ double sbb[8];
+        abb = warp_sum(abb);
+        if ((threadIdx.x & 31) == 0) sbb[threadIdx.x >> 5] = abb;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double b = 0;
+            for (int q = 0; q < (int)(blockDim.x >> 5); ++q) b += sbb[q];
+            S->partial[1][blockIdx.x] = b;
+        }
+    }
+    if (block_sum_last(arr, S, 0, tot_rr)) {
+        if ((threadIdx.x >> 5) == 0) {
+            const int lane = threadIdx.x & 31;
+            double s = 0;
+            for (int q = lane; q < (int)gridDim.x; q += 32) s += __ldcg(&S->partial[1][q]);
+            tot_bb = warp_sum(s);
+            if (lane == 0) {
+                S->rr = tot_rr; S->rr_old = tot_rr; S->bb = tot_bb; S->dw = 0;
+                S->iters = 0;
+                S->done = (tot_rr <= S->tol2 * tot_bb) ? 1 : 0;
+            }
+        }
+    }
+}
+
+template <class Real, int V>
+__global__ void __launch_bounds__(256) k_cg_dir_matvec(Grid g, CgScal* S, const Real* __restrict__ r, const Real* __restrict__ d,
+                                                       Real* __restrict__ dn, Real* __restrict__ w) {
+    if (S->done) return;
+    const Real beta = (S->iters == 0) ? Real(0) : (Real)(S->rr / S->rr_old);
+    const int ZV = g.Z / V;
+    const long long nvec = (long long)(g.j1 - g.j0) * g.X * ZV;
+    double acc = 0;
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < nvec; t += (long long)gridDim.x * blockDim.x) {
+        int i, j, k; long long c;
+        vec_cell<Real, V>(g, t, ZV, i, j, k, c);
+        const Pack<Real, V> rc = ldp<Real, V>(r + c), dc = ldp<Real, V>(d + c);
+        Real ctr[V], sum[V];
+#pragma unroll
+        for (int a = 0; a < V; ++a) { ctr[a] = rfma(beta, dc.a[a], rc.a[a]); sum[a] = Real(0); }
+#define INK_NBR(cond, off)                                                                  \
+        if (cond) {                                                                         \
+            const Pack<Real, V> qr = ldp<Real, V>(r + c + (off)), qd = ldp<Real, V>(d + c + (off)); \
+            _Pragma("unroll") for (int a = 0; a < V; ++a) sum[a] += rfma(beta, qd.a[a], qr.a[a]);   \
+        }
+        INK_NBR(i + 1 < g.X, g.sx)
+        INK_NBR(i - 1 >= 0, -(long long)g.sx)
+        INK_NBR(j + 1 < g.Y, g.sy)
+        INK_NBR(j - 1 >= 0, -g.sy)
+#undef INK_NBR
+        const Real zl = (k > 0) ? rfma(beta, d[c - 1], r[c - 1]) : Real(0);
+        const Real zr = (k + V < g.Z) ? rfma(beta, d[c + V], r[c + V]) : Real(0);
+        Pack<Real, V> wc, dnc;
+#pragma unroll
+        for (int a = 0; a < V; ++a) {
+            const Real left = (a > 0) ? ctr[a > 0 ? a - 1 : 0] : zl;
+            const Real right = (a < V - 1) ? ctr[a < V - 1 ? a + 1 : 0] : zr;
+            wc.a[a] = Real(6) * ctr[a] - (sum[a] + left + right);
+            dnc.a[a] = ctr[a];
+            acc += (double)ctr[a] * (double)wc.a[a];
+        }
+        stp<Real, V>(dn + c, dnc);
+        stp<Real, V>(w + c, wc);
+    }
+    double tot;
+    if (block_sum_last(acc, S, 0, tot)) {
+        if (threadIdx.x == 0) S->dw = tot;
+    }
+}
+
+template <class Real, int V>
+__global__ void __launch_bounds__(256) k_cg_update(Grid g, CgScal* S, Real* __restrict__ x, Real* __restrict__ r, const Real* __restrict__ d,
+                                                   const Real* __restrict__ w) {
+    if (S->done) return;
+    const Real alpha = (Real)(S->rr / S->dw);
+    const int ZV = g.Z / V;
+    const long long nvec = (long long)(g.j1 - g.j0) * g.X * ZV;
+    const long long base = (long long)g.j0 * g.sy;
+    double acc = 0;
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < nvec; t += (long long)gridDim.x * blockDim.x) {
+        const long long c = base + t * V;
+        Pack<Real, V> xc = ldp<Real, V>(x + c), rc = ldp<Real, V>(r + c);
+        const Pack<Real, V> dc = ldp<Real, V>(d + c), wc = ldp<Real, V>(w + c);
+#pragma unroll
+        for (int a = 0; a < V; ++a) {
+            xc.a[a] = rfma(alpha, dc.a[a], xc.a[a]);
+            rc.a[a] = rfma(-alpha, wc.a[a], rc.a[a]);
+            acc += (double)rc.a[a] * (double)rc.a[a];
+        }
+        stp<Real, V>(x + c, xc);
+        stp<Real, V>(r + c, rc);
+    }
+    double tot;
+    if (block_sum_last(acc, S, 1, tot)) {
+        if (threadIdx.x == 0) {
+            S->rr_old = S->rr;
+            S->rr = tot;
+            S->iters += 1;
+            if (tot <= S->tol2 * S->bb) S->done = 1;
+        }
+    }
+}
+
+}  // namespace ink

@@ -1,0 +1,259 @@
+"""Host-side mirror of the reference's `System` (src/system.h:70-138) over the C ABI.
+
+`System` keeps the reference's method names (`init`, `solve`, `getInkParticles`, `getWaterGrid`, `checkNanAndInf`)
+and adds the per-phase hooks the parity tests need (same names as oracle.OracleSystem / RefSystem so a test reads
+the same against all three).  All compute happens in libinkb200.so on the GPU; this file only marshals numpy arrays.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+
+import numpy as np
+
+from . import _capi
+
+
+@dataclass
+class Params:
+    """The global constants of reference src/system.h:13-38 (defaults = committed values)."""
+
+    cell_dim: float = 1.0
+    density: float = 0.95
+    k_vort: float = 1.0
+    viscosity: float = 1.0016
+    p_atm: float = 1.0
+    gravity: tuple = (0.0, -0.1, 0.0)
+    k_cfl: float = 0.2
+    dt_min: float = 0.005
+    dt_max: float = 1.0
+    buffer_size: int = 3
+
+
+class InkError(RuntimeError):
+    pass
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data_as(C.c_void_p)
+    if hasattr(a, "data_ptr"):  # torch tensor (host pinned or device) — plumbing only
+        return C.c_void_p(a.data_ptr())
+    return C.c_void_p(int(a))
+
+
+class System:
+    """Drop-in for the reference `System`: one MAC water grid + ink particle drops, stepped on one B200."""
+
+    def __init__(self, X=20, Y=45, Z=20, dtype=np.float32, params: Params | None = None, arith="strict", device=0,
+                 cg_rtol=None, cg_max_iters=None, cg_check_every=None, cg_warm_start=None, cg_precond=None,
+                 resort_interval=None):
+        self.L = _capi.load()
+        self.dims = (int(X), int(Y), int(Z))
+        self.dtype = np.dtype(dtype)
+        if self.dtype not in (np.dtype(np.float32), np.dtype(np.float64)):
+            raise ValueError("dtype must be float32 or float64")
+        self.hd = 32 if self.dtype == np.float32 else 64
+        self.params = params or Params()
+        p = _capi.default_params()
+        q = self.params
+        p.X, p.Y, p.Z = self.dims
+        p.cell_dim, p.density, p.k_vort, p.viscosity, p.p_atm = q.cell_dim, q.density, q.k_vort, q.viscosity, q.p_atm
+        p.gravity[0], p.gravity[1], p.gravity[2] = q.gravity
+        p.k_cfl, p.dt_min, p.dt_max, p.buffer_size = q.k_cfl, q.dt_min, q.dt_max, q.buffer_size
+        p.precision = self.hd
+        p.arith = {"strict": _capi.ARITH_STRICT, "fast": _capi.ARITH_FAST}[arith]
+        p.device = device
+        if cg_rtol is not None:
+            p.cg_rtol = cg_rtol
+        if cg_max_iters is not None:
+            p.cg_max_iters = cg_max_iters
+        if cg_check_every is not None:
+            p.cg_check_every = cg_check_every
+        if cg_warm_start is not None:
+            p.cg_warm_start = int(cg_warm_start)
+        if cg_precond is not None:
+            p.cg_precond = {"none": _capi.PCG_NONE, "mg": _capi.PCG_MG}[cg_precond]
+        if resort_interval is not None:
+            p.resort_interval = resort_interval
+        self._p = p
+        h = C.c_void_p()
+        rc = self.L.ink_create(C.byref(p), C.byref(h))
+        if rc != 0:
+            raise InkError(f"ink_create failed ({rc}): {self.L.ink_last_error(None).decode()}")
+        self.h = h
+
+    # ---- lifetime
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.ink_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise InkError(self.L.ink_last_error(self.h).decode())
+
+    def _a(self, x):
+        return np.ascontiguousarray(x, dtype=self.dtype)
+
+    # ---- reference API (src/system.h:75-81)
+    def init(self):
+        """System::init (src/system.cpp:10-26): the grid is created zeroed by the constructor; particle seeding is the
+        caller's job here (set_particles) — the emitter/box seeders are host-side helpers in ink_simulation_b200.seeding."""
+        return self
+
+    def solve(self, timeToNextRender):
+        dt = C.c_double()
+        self._ck(self.L.ink_step(self.h, float(timeToNextRender), C.byref(dt)))
+        return dt.value
+
+    def getInkParticles(self):
+        """list over drops of (positions (N,3), velocities (N,3)) in the caller's particle order."""
+        return [self.get_particles(d) for d in range(self.num_drops())]
+
+    def getWaterGrid(self):
+        """currVelocity of every cell as three dense (X,Y,Z) arrays."""
+        return self.get_field("curr")
+
+    def checkNanAndInf(self):
+        u, v, w = self.get_field("curr")
+        for a in (u, v, w):
+            assert np.isfinite(a).all()
+        for pos, vel in self.getInkParticles():
+            assert np.isfinite(pos).all() and np.isfinite(vel).all()
+
+    # ---- state
+    def set_particles(self, pos, vel=None, drop=0):
+        if hasattr(pos, "data_ptr"):  # torch tensor: float32/float64, contiguous (N,3)
+            n = pos.shape[0]
+            hd = 32 if pos.element_size() == 4 else 64
+            self._ck(self.L.ink_set_particles(self.h, drop, _ptr(pos), _ptr(vel), n, hd))
+            return
+        pos = self._a(pos).reshape(-1, 3)
+        v = None if vel is None else self._a(vel).reshape(-1, 3)
+        self._ck(self.L.ink_set_particles(self.h, drop, _ptr(pos), _ptr(v), len(pos), self.hd))
+
+    def num_drops(self):
+        return int(self.L.ink_num_drops(self.h))
+
+    def num_particles(self, drop=0):
+        return int(self.L.ink_num_particles(self.h, drop))
+
+    def get_particles(self, drop=0, out_pos=None, out_vel=None):
+        if out_pos is not None or out_vel is not None:  # caller-provided buffers (numpy or torch, host or device)
+            t = out_pos if out_pos is not None else out_vel
+            hd = (32 if t.element_size() == 4 else 64) if hasattr(t, "data_ptr") else (32 if t.dtype == np.float32 else 64)
+            self._ck(self.L.ink_get_particles(self.h, drop, _ptr(out_pos), _ptr(out_vel), hd))
+            return out_pos, out_vel
+        n = self.num_particles(drop)
+        pos = np.empty((n, 3), self.dtype)
+        vel = np.empty((n, 3), self.dtype)
+        self._ck(self.L.ink_get_particles(self.h, drop, _ptr(pos), _ptr(vel), self.hd))
+        return pos, vel
+
+    def set_velocity(self, u, v, w):
+        u, v, w = self._a(u), self._a(v), self._a(w)
+        assert u.shape == self.dims and v.shape == self.dims and w.shape == self.dims
+        self._ck(self.L.ink_set_velocity(self.h, _ptr(u), _ptr(v), _ptr(w), self.hd))
+
+    def get_field(self, which="curr"):
+        idx = {"old": 0, "curr": 1, "curl": 2}[which]
+        out = [np.empty(self.dims, self.dtype) for _ in range(3)]
+        self._ck(self.L.ink_get_field(self.h, idx, *[_ptr(a) for a in out], self.hd))
+        return out
+
+    def get_velocity(self):
+        return self.get_field("curr")
+
+    def get_pressure(self):
+        p = np.empty(self.dims, self.dtype)
+        self._ck(self.L.ink_get_pressure(self.h, _ptr(p), self.hd))
+        return p
+
+    def set_pressure(self, p):
+        p = self._a(p)
+        assert p.shape == self.dims
+        self._ck(self.L.ink_set_pressure(self.h, _ptr(p), self.hd))
+
+    def get_mark(self):
+        m = np.empty(self.dims, np.uint8)
+        self._ck(self.L.ink_get_mark(self.h, _ptr(m)))
+        return m
+
+    # ---- phases (each followed by the reference's old = curr commit)
+    def calc_dt(self, ttnr):
+        dt = C.c_double()
+        self._ck(self.L.ink_calc_dt(self.h, float(ttnr), C.byref(dt)))
+        return dt.value
+
+    def advect(self, dt):
+        self._ck(self.L.ink_advect(self.h, float(dt)))
+
+    def forces(self, dt, return_mark=False):
+        self._ck(self.L.ink_forces(self.h, float(dt)))
+        return self.get_mark() if return_mark else None
+
+    def viscosity(self, dt):
+        self._ck(self.L.ink_viscosity(self.h, float(dt)))
+
+    def pressure_rhs(self, dt):
+        b = np.empty(self.dims, self.dtype)
+        self._ck(self.L.ink_pressure_rhs(self.h, float(dt), _ptr(b), self.hd))
+        return b
+
+    def pressure(self, dt):
+        self._ck(self.L.ink_pressure(self.h, float(dt)))
+
+    def pressure_given_p(self, dt, p):
+        self.set_pressure(p)
+        self._ck(self.L.ink_pressure_given_p(self.h, float(dt)))
+
+    def poisson_solve(self, b):
+        b = self._a(b)
+        p = np.empty(self.dims, self.dtype)
+        self._ck(self.L.ink_poisson_solve(self.h, _ptr(b), _ptr(p), self.hd))
+        return p, self.stats().cg_rel_residual
+
+    def vorticity(self, dt):
+        self._ck(self.L.ink_vorticity(self.h, float(dt)))
+
+    def divergence(self):
+        d = np.empty(self.dims, self.dtype)
+        self._ck(self.L.ink_get_divergence(self.h, _ptr(d), self.hd))
+        return d
+
+    def sample_velocity(self, pos):
+        pos = self._a(pos).reshape(-1, 3)
+        out = np.empty_like(pos)
+        self._ck(self.L.ink_sample_velocity(self.h, _ptr(pos), len(pos), _ptr(out), self.hd))
+        return out
+
+    def velocity_field_update(self, dt):
+        self._ck(self.L.ink_velocity_field_update(self.h, float(dt)))
+
+    def particles(self, dt):
+        self._ck(self.L.ink_particles(self.h, float(dt)))
+
+    def resort_particles(self):
+        self._ck(self.L.ink_resort_particles(self.h))
+
+    def sync(self):
+        self._ck(self.L.ink_sync(self.h))
+
+    def stats(self) -> _capi.InkStats:
+        s = _capi.InkStats()
+        self._ck(self.L.ink_get_stats(self.h, C.byref(s)))
+        return s
+
+    def phase_ms(self):
+        out = (C.c_float * 8)()
+        self._ck(self.L.ink_get_phase_ms(self.h, out))
+        return dict(zip(("dt", "advect", "forces", "viscosity", "pressure", "vorticity", "particles", "resort"), list(out)))

@@ -142,7 +142,10 @@ struct Oracle {
         if (maxVelocity == 0) return P.dt_min;
         float timeStep = P.k_cfl * (P.cell_dim / maxVelocity);
         timeStep = std::max(std::min(timeStep, P.dt_max), P.dt_min);
-        return std::min(timeToNextRender, (double)timeStep);
+        // `timeStep = std::min(timeToNextRender, (double)timeStep)` assigns to the FLOAT local (src/waterSolver.cpp:35):
+        // the returned step is narrowed to float even when timeToNextRender wins
+        timeStep = (float)std::min(timeToNextRender, (double)timeStep);
+        return timeStep;
     }
 
     // src/waterSolver.cpp:98-128 (Q6, Q7): RK2 back-trace of the cell centre, nearest-cell copy of

@@ -1,0 +1,61 @@
+"""-m "not gpu": pins the CPU oracle (oracle/ink_oracle.cpp) against the golden vectors generated from the
+compiled reference (tests/golden/make_golden.py), and — where oracle/_ref/libinkref.so exists — against the
+compiled reference run live on fresh seeded inputs."""
+import numpy as np
+import pytest
+
+import parity
+import util
+
+
+@pytest.mark.parametrize("path", parity.GOLDEN, ids=lambda p: p.split("ref_")[-1][:-4])
+def test_oracle_matches_golden_bit_exact(oracle_mod, path):
+    G = parity.load(path)
+    parity.check_phases_exact(lambda d: oracle_mod.OracleSystem(*d, dtype=np.float32), G)
+
+
+@pytest.mark.parametrize("path", parity.GOLDEN, ids=lambda p: p.split("ref_")[-1][:-4])
+def test_oracle_pressure_and_solve_vs_golden(oracle_mod, path):
+    G = parity.load(path)
+    mk = lambda d: oracle_mod.OracleSystem(*d, dtype=np.float32)  # noqa: E731
+    parity.check_pressure(mk, G)
+    parity.check_solve(mk, G)
+
+
+def test_oracle_fp64_close_to_fp32_reference(oracle_mod):
+    """The fp64 oracle (what the GPU fp64 mode is compared with) stays within fp32 round-off of the reference."""
+    G = parity.load(parity.GOLDEN[0])
+    dims = tuple(int(x) for x in G["dims"])
+    S = oracle_mod.OracleSystem(*dims, dtype=np.float64)
+    S.set_velocity(G["u"], G["v"], G["w"]); S.set_particles(G["part"])
+    S.particles(0.2)
+    pos = S.get_particles()[0]
+    ref = G["particles_pos"]
+    assert np.max(np.abs(pos - ref) / np.maximum(np.abs(ref), 1.0)) < 1e-6
+
+
+def test_oracle_poisson_is_exact(oracle_mod):
+    """The DST-I solve reproduces A p = b to fp64 round-off (A: diag -6, +1 per in-grid neighbour)."""
+    for dims in (util.C1, util.ODD, util.RECT):
+        S = oracle_mod.OracleSystem(*dims, dtype=np.float64)
+        b = np.random.default_rng(5).normal(size=dims)
+        p, res = S.poisson_solve(b)
+        assert res < 1e-12
+
+
+@pytest.mark.skipif(not __import__("oracle").have_ref(), reason="compiled reference not built here")
+def test_oracle_vs_live_reference_random_states(oracle_mod):
+    """Fresh seeds (not the committed fixtures): oracle == compiled reference bit for bit, phase by phase."""
+    for seed, dims in ((101, util.C1), (202, (10, 12, 10))):
+        u, v, w = util.rand_field(dims, seed, scale=0.8)
+        part = util.wild_particles(dims, 300, seed + 1)
+        for phase, dt in (("advect", 0.7), ("forces", 0.3), ("viscosity", 0.2), ("vorticity", 0.2), ("particles", 0.3)):
+            R = oracle_mod.RefSystem(*dims)
+            O = oracle_mod.OracleSystem(*dims, dtype=np.float32)
+            for S in (R, O):
+                S.set_velocity(u, v, w)
+                S.set_particles(part if phase != "forces" else util.uniform_particles(dims, 40, seed))
+                getattr(S, phase)(dt)
+            assert np.array_equal(np.stack(R.get_velocity()), np.stack(O.get_velocity())), phase
+            assert np.array_equal(R.get_particles()[0], O.get_particles()[0]), phase
+            R.close()
