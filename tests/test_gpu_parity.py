@@ -97,14 +97,19 @@ def test_gpu_projection_vs_oracle(oracle_mod, dims, dtype):
 @pytest.mark.parametrize("dtype", [np.float32, np.float64], ids=["fp32", "fp64"])
 def test_gpu_full_steps_track_oracle_per_step(oracle_mod, dtype):
     """20 System::solve steps of BASELINE config 1 (8x25x8, 10k particles in the initParticles box); after every step the
-    GPU state is compared with the oracle stepped from the SAME input state (then the oracle state is adopted)."""
+    GPU state is compared with the oracle stepped from the SAME input state (then the oracle state is adopted).
+
+    End-of-step tolerance in fp32: the vorticity-confinement phase divides grad|curl| by |curl_cell| (Q11); where the
+    field is round-off noise this normalisation amplifies 1e-7 differences to ~1e-4 of the field scale — the same
+    spread separates the reference arithmetic in fp32 from itself in fp64 (see test_gpu_step_phase_by_phase, which
+    shows every phase but the solve is bit-exact and the PROJECTED field is within 1e-5).  fp64 mode is tight."""
     dims = util.C1
     part = util.box_particles(dims, 10000, 1, dtype=dtype)
     S = gpu(dims, dtype)
     S.set_particles(part)
     O = oracle_mod.OracleSystem(*dims, dtype=dtype)
     O.set_particles(part)
-    ptol, vtol = (1e-6, 1e-5)
+    ptol, vtol = (1e-6, 5e-4) if dtype == np.float32 else (1e-9, 1e-8)
     for step in range(20):
         dt_o = O.solve(0.35)
         dt_s = S.solve(0.35)
@@ -116,6 +121,35 @@ def test_gpu_full_steps_track_oracle_per_step(oracle_mod, dtype):
         # re-synchronise: identical input state for the next step
         S.set_velocity(*O.get_velocity())
         S.set_particles(po, O.get_particles()[1])
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64], ids=["fp32", "fp64"])
+def test_gpu_step_phase_by_phase(oracle_mod, dtype):
+    """One developing scene (config 1), 12 steps, checked PHASE BY PHASE from identical input: convection, forces,
+    viscosity bit-exact; projected velocity within 1e-5 of the field scale with divergence no worse than the exact
+    solve's (north_star); then — from the oracle's projected field — vorticity and particles bit-exact."""
+    dims = util.C1
+    part = util.box_particles(dims, 10000, 1, dtype=dtype)
+    S = gpu(dims, dtype)
+    O = oracle_mod.OracleSystem(*dims, dtype=dtype)
+    for T in (S, O):
+        T.set_particles(part)
+    for step in range(12):
+        dt = O.calc_dt(0.35)
+        assert S.calc_dt(0.35) == dt
+        for ph in ("advect", "forces", "viscosity"):
+            getattr(O, ph)(dt); getattr(S, ph)(dt)
+            assert np.array_equal(np.stack(O.get_velocity()), np.stack(S.get_velocity())), (step, ph)
+        O.pressure(dt); S.pressure(dt)
+        vo, vs = np.stack(O.get_velocity()), np.stack(S.get_velocity())
+        assert util.rel_inf(vs, vo) < (1e-5 if dtype == np.float32 else 1e-9), (step, util.rel_inf(vs, vo))
+        assert np.abs(S.divergence()).max() <= np.abs(O.divergence()).max() * 1.001 + 1e-5 * np.abs(vo).max()
+        S.set_velocity(*O.get_velocity())          # identical input for the phases after the solve
+        O.vorticity(dt); S.vorticity(dt)
+        assert np.array_equal(np.stack(O.get_velocity()), np.stack(S.get_velocity())), (step, "vorticity")
+        O.particles(dt); S.particles(dt)
+        assert np.array_equal(O.get_particles()[0], S.get_particles()[0]), (step, "particles")
+        assert np.array_equal(O.get_particles()[1], S.get_particles()[1]), (step, "particle velocities")
 
 
 @pytest.mark.parametrize("dtype", [np.float32, np.float64], ids=["fp32", "fp64"])
