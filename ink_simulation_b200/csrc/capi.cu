@@ -644,8 +644,11 @@ struct Ctx final : CtxBase {
     int particles_impl(Real dt) {
         if (np == 0) return 0;
         CK(cudaMemsetAsync(seed, 0, g.n, stream));
-        if (P.arith == INK_ARITH_FAST) LAUNCH((k_particles_rk2<Real, true>), nblk(np), 256, g, C, dt, np, part[pcur], U(0), U(1), U(2), seed);
-        else LAUNCH((k_particles_rk2<Real, false>), nblk(np), 256, g, C, dt, np, part[pcur], U(0), U(1), U(2), seed);
+        const bool fast = P.arith == INK_ARITH_FAST, uh = C.unit_h && g.n < (1ll << 31);
+#define INK_K8(F, H) LAUNCH((k_particles_rk2<Real, F, H>), nblk(np), 256, g, C, dt, np, part[pcur], U(0), U(1), U(2), seed)
+        if (fast) { if (uh) INK_K8(true, true); else INK_K8(true, false); }
+        else { if (uh) INK_K8(false, true); else INK_K8(false, false); }
+#undef INK_K8
         CK(cudaGetLastError());
         // K8 seeded the mask from the new positions, and the wall clamp put every particle inside the grid; phantom
         // cells created earlier persist in the reference's map (their velocity keeps entering calcTimeStep)

@@ -9,6 +9,7 @@
 #pragma once
 #include "common.cuh"
 #include "grid_kernels.cuh"
+#include "sample3.cuh"
 
 namespace ink {
 
@@ -39,7 +40,7 @@ __device__ __forceinline__ bool cell_of_point(const Grid& g, Real x, Real y, Rea
 // cell of the NEW position: it is what the next step's applyExternalForces sees, src/waterSolver.cpp:161-163).
 // Algorithmic traffic: read pos 3R, write pos 3R, write vel 3R (R = sizeof(Real)) + the velocity field once.
 // ------------------------------------------------------------------------------------------------
-template <class Real, bool FAST>
+template <class Real, bool FAST, bool UNIT_H>
 __global__ void __launch_bounds__(256) k_particles_rk2(Grid g, Consts<Real> C, Real dt, long long n, Particles<Real> P,
                                                        const Real* __restrict__ u, const Real* __restrict__ v, const Real* __restrict__ w,
                                                        uint8_t* __restrict__ seed) {
@@ -47,10 +48,10 @@ __global__ void __launch_bounds__(256) k_particles_rk2(Grid g, Consts<Real> C, R
     if (s >= n) return;
     Real x = ld_stream(P.p[0] + s), y = ld_stream(P.p[1] + s), z = ld_stream(P.p[2] + s);
     Real sx, sy, sz;
-    get_velocity<Real, FAST>(u, v, w, g, C, x, y, z, sx, sy, sz);
+    get_velocity3<Real, FAST, UNIT_H>(u, v, w, g, C, x, y, z, sx, sy, sz);
     Real vx = C.rho * sx, vy = C.rho * sy, vz = C.rho * sz;                       // equation 9
     const Real mx = x + (vx * dt * Real(.5)), my = y + (vy * dt * Real(.5)), mz = z + (vz * dt * Real(.5));  // equation 7
-    get_velocity<Real, FAST>(u, v, w, g, C, mx, my, mz, sx, sy, sz);
+    get_velocity3<Real, FAST, UNIT_H>(u, v, w, g, C, mx, my, mz, sx, sy, sz);
     const Real wx = C.rho * sx, wy = C.rho * sy, wz = C.rho * sz;
     x = mx + (dt * wx); y = my + (dt * wy); z = mz + (dt * wz);                  // equation 8 (from the MIDPOINT, Q3)
     if (x < Real(0) || x > C.bx) { vx *= Real(-1.f); x = rmin(rmax(x, C.lo), C.cx); }
@@ -58,8 +59,14 @@ __global__ void __launch_bounds__(256) k_particles_rk2(Grid g, Consts<Real> C, R
     if (z < Real(0) || z > C.bz) { vz *= Real(-1.f); z = rmin(rmax(z, C.lo), C.cz); }
     st_stream(P.p[0] + s, x); st_stream(P.p[1] + s, y); st_stream(P.p[2] + s, z);
     st_stream(P.v[0] + s, vx); st_stream(P.v[1] + s, vy); st_stream(P.v[2] + s, vz);
-    long long c;
-    if (cell_of_point(g, x, y, z, c)) seed[c] = 1;
+    if (UNIT_H) {   // launcher guarantees X*Y*Z < 2^31 here: 32-bit cell index; same test as cell_of_point
+        const int ci = (int)rfloor(x), cj = (int)rfloor(y), ck = (int)rfloor(z);
+        if ((unsigned)ci < (unsigned)g.X && (unsigned)cj < (unsigned)g.Y && (unsigned)ck < (unsigned)g.Z)
+            seed[(cj * g.X + ci) * g.Z + ck] = 1;
+    } else {
+        long long c;
+        if (cell_of_point(g, x, y, z, c)) seed[c] = 1;
+    }
 }
 
 // K2a stand-alone: seed mask from the current positions (after ink_set_particles); counts out-of-grid particles.
