@@ -15,6 +15,7 @@
 #include "cg.cuh"
 #include "common.cuh"
 #include "grid_kernels.cuh"
+#include "mg.cuh"
 #include "particle_kernels.cuh"
 
 namespace ink {
@@ -84,6 +85,14 @@ struct Ctx final : CtxBase {
     Real* curl[3] = {nullptr, nullptr, nullptr};
     Real *pres = nullptr, *q = nullptr, *rhs = nullptr, *cg_r = nullptr, *cg_d[2] = {nullptr, nullptr}, *cg_w = nullptr;
     bool have_q = false;
+    // multigrid preconditioner (mg.cuh): lv[0..lt) run as global-memory kernels, the rest inside k_mg_tail
+    std::vector<MgLevelPtrs<Real>> lv;
+    std::vector<Real*> mg_alloc;
+    int mg_lt = 0;
+    MgTailArgs mg_tail{};
+    size_t mg_tail_smem = 0;
+    bool use_mg = false;
+    int prev_iters = 0;
     CgScal* S = nullptr;
     CgScal* hS = nullptr;  // pinned mirror of the scalar head
     uint8_t *seed = nullptr, *mark = nullptr;
@@ -113,6 +122,7 @@ struct Ctx final : CtxBase {
             for (auto& p : b) cudaFree(p);
         for (auto& p : curl) cudaFree(p);
         cudaFree(pres); cudaFree(q); cudaFree(rhs); cudaFree(cg_r); cudaFree(cg_d[0]); cudaFree(cg_d[1]); cudaFree(cg_w);
+        for (auto p : mg_alloc) cudaFree(p);
         cudaFree(S); cudaFreeHost(hS); cudaFree(seed); cudaFree(mark); cudaFree(d_scal); cudaFreeHost(h_scal);
         free_particles();
         cudaFree(bin_count);
@@ -175,6 +185,8 @@ struct Ctx final : CtxBase {
             scan_n.push_back(m);
         }
         for (auto& e : ev) CK(cudaEventCreate(&e));
+        if (P.cg_precond == INK_PCG_MG)
+            if (int rc = mg_setup()) return rc;
         maxv_valid = true;  // zero field: max speed bits already 0
         seed_valid = true;
         CK(cudaStreamSynchronize(stream));
@@ -550,7 +562,82 @@ struct Ctx final : CtxBase {
         return grid_out_any(rhs, b, hd);
     }
 
-    // solve M x = f (M = -A) by CG; x holds the initial guess
+    // ---- multigrid hierarchy ------------------------------------------------------------------------
+    int mg_setup() {
+        const size_t smem_cap = 200 * 1024;
+        std::vector<MgDims> abs_d;
+        abs_d.push_back(MgDims{g.X, g.Y, g.Z, g.j0, g.j1});
+        auto cells_local = [](const MgDims& d) { return (long long)d.X * (d.j1 - d.j0) * d.Z; };
+        // tail = local-coordinate levels below (and including) some level; find the first level whose tail fits in shared memory
+        auto build_tail = [&](const MgDims& top, MgTailArgs& T) -> size_t {
+            MgDims d{top.X, top.j1 - top.j0, top.Z, 0, top.j1 - top.j0};
+            T.nlev = 0;
+            long long total = 0;
+            while (true) {
+                T.d[T.nlev++] = d;
+                total += 3ll * d.X * d.Y * d.Z;
+                if ((long long)d.X * d.Y * d.Z <= 16 || T.nlev == kMgMaxLevels) break;
+                d = MgDims{(d.X + 1) / 2, (d.Y + 1) / 2, (d.Z + 1) / 2, 0, (d.Y + 1) / 2};
+            }
+            return (size_t)total * sizeof(Real);
+        };
+        while (true) {
+            mg_tail_smem = build_tail(abs_d.back(), mg_tail);
+            if (mg_tail_smem <= smem_cap) break;
+            if ((int)abs_d.size() >= kMgMaxLevels) { err = "multigrid: grid too large for the level budget"; return 2; }
+            const MgDims& d = abs_d.back();
+            abs_d.push_back(MgDims{(d.X + 1) / 2, (d.Y + 1) / 2, (d.Z + 1) / 2, d.j0 >> 1, (d.j1 + 1) >> 1});
+            (void)cells_local;
+        }
+        mg_lt = (int)abs_d.size() - 1;
+        mg_tail.s0 = (float)(1 << mg_lt);
+        mg_tail.final_dot = (mg_lt == 0) ? 1 : 0;
+        lv.resize(abs_d.size());
+        for (size_t l = 0; l < abs_d.size(); ++l) {
+            lv[l].d = abs_d[l];
+            lv[l].s = (Real)(1 << l);
+            const size_t nb = (size_t)abs_d[l].X * abs_d[l].Y * abs_d[l].Z * sizeof(Real);
+            Real** slots[3] = {&lv[l].xa, &lv[l].xb, &lv[l].r};
+            for (int a = 0; a < 3; ++a) {
+                *slots[a] = nullptr;
+                if (a == 2 && l == 0) continue;           // level-0 rhs is the CG residual itself
+                if (a == 1 && (int)l == mg_lt) continue;  // the tail's top level only needs its result buffer
+                CK(cudaMalloc(slots[a], nb));
+                CK(cudaMemsetAsync(*slots[a], 0, nb, stream));
+                mg_alloc.push_back(*slots[a]);
+            }
+        }
+        CK(cudaFuncSetAttribute(k_mg_tail<Real>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mg_tail_smem));
+        use_mg = true;
+        return 0;
+    }
+    static unsigned int mg_blocks(const MgDims& d) {
+        const long long n = (long long)d.X * (d.j1 - d.j0) * d.Z;
+        return (unsigned int)std::min<long long>(kMgBlocks, std::max<long long>(1, (n + 255) / 256));
+    }
+    // z = B r : one V-cycle; the result is lv[0].xa; the last kernel also sets S->rz_old, S->rz = <r, z>
+    int mg_vcycle(const Real* r0) {
+        auto rhs = [&](int l) -> const Real* { return l == 0 ? r0 : lv[l].r; };
+        for (int l = 0; l < mg_lt; ++l) {
+            LAUNCH((k_mg_presmooth<Real>), mg_blocks(lv[l].d), 256, S, lv[l].d, lv[l].s, rhs(l), lv[l].xa);
+            LAUNCH((k_mg_residual_restrict<Real>), mg_blocks(lv[l + 1].d), 256, S, lv[l].d, lv[l + 1].d, lv[l].s, rhs(l), lv[l].xa, lv[l + 1].r);
+        }
+        {
+            const MgDims& d = lv[mg_lt].d;
+            const long long off = (long long)d.j0 * d.X * d.Z;
+            k_mg_tail<Real><<<1, kMgTailThreads, mg_tail_smem, stream>>>(S, mg_tail, rhs(mg_lt) + off, lv[mg_lt].xa + off);
+            ++stats.kernel_launches;
+        }
+        for (int l = mg_lt - 1; l >= 0; --l) {
+            LAUNCH((k_mg_prolong_smooth<Real>), mg_blocks(lv[l].d), 256, S, lv[l].d, lv[l + 1].d, lv[l].s, rhs(l), lv[l].xa, lv[l + 1].xa, lv[l].xb);
+            if (l == 0) LAUNCH((k_mg_smooth<Real, true>), mg_blocks(lv[l].d), 256, S, lv[l].d, lv[l].s, rhs(l), lv[l].xb, lv[l].xa);
+            else LAUNCH((k_mg_smooth<Real, false>), mg_blocks(lv[l].d), 256, S, lv[l].d, lv[l].s, rhs(l), lv[l].xb, lv[l].xa);
+        }
+        CK(cudaGetLastError());
+        return 0;
+    }
+
+    // solve M x = f (M = -A) by (preconditioned) CG; x holds the initial guess
     int cg_solve(const Real* f, Real* x) {
         const unsigned int nb = cg_blocks();
         const double tol2 = P.cg_rtol * P.cg_rtol;
@@ -567,17 +654,29 @@ struct Ctx final : CtxBase {
             return 0;
         }
         int dcur = 0, launched = 0;
-        const int every = std::max(1, P.cg_check_every);
+        const Real* zsrc = cg_r;
+        if (use_mg) {
+            if (int rc = mg_vcycle(cg_r)) return rc;
+            zsrc = lv[0].xa;
+        }
+        // host polls convergence every `every` iterations; kernels launched after convergence are no-ops (S->done).
+        // With the preconditioner the count is small and steady from step to step: launch last solve's count first.
+        const int every = use_mg ? 2 : std::max(1, P.cg_check_every);
         while (!hS->done && launched < P.cg_max_iters) {
-            const int batch = std::min(every, P.cg_max_iters - launched);
+            int batch = std::min(every, P.cg_max_iters - launched);
+            if (use_mg && launched == 0 && prev_iters > 1) batch = std::min(prev_iters, P.cg_max_iters);
             for (int it = 0; it < batch; ++it) {
                 if (vec4()) {
-                    LAUNCH((k_cg_dir_matvec<Real, 4>), nb, 256, g, S, cg_r, cg_d[dcur], cg_d[dcur ^ 1], cg_w);
-                    LAUNCH((k_cg_update<Real, 4>), nb, 256, g, S, x, cg_r, cg_d[dcur ^ 1], cg_w);
+                    LAUNCH((k_cg_dir_matvec<Real, 4>), nb, 256, g, S, zsrc, cg_d[dcur], cg_d[dcur ^ 1], cg_w);
+                    if (use_mg) LAUNCH((k_cg_update<Real, 4, true>), nb, 256, g, S, x, cg_r, cg_d[dcur ^ 1], cg_w);
+                    else LAUNCH((k_cg_update<Real, 4, false>), nb, 256, g, S, x, cg_r, cg_d[dcur ^ 1], cg_w);
                 } else {
-                    LAUNCH((k_cg_dir_matvec<Real, 1>), nb, 256, g, S, cg_r, cg_d[dcur], cg_d[dcur ^ 1], cg_w);
-                    LAUNCH((k_cg_update<Real, 1>), nb, 256, g, S, x, cg_r, cg_d[dcur ^ 1], cg_w);
+                    LAUNCH((k_cg_dir_matvec<Real, 1>), nb, 256, g, S, zsrc, cg_d[dcur], cg_d[dcur ^ 1], cg_w);
+                    if (use_mg) LAUNCH((k_cg_update<Real, 1, true>), nb, 256, g, S, x, cg_r, cg_d[dcur ^ 1], cg_w);
+                    else LAUNCH((k_cg_update<Real, 1, false>), nb, 256, g, S, x, cg_r, cg_d[dcur ^ 1], cg_w);
                 }
+                if (use_mg)
+                    if (int rc = mg_vcycle(cg_r)) return rc;
                 dcur ^= 1;
             }
             launched += batch;
@@ -585,6 +684,7 @@ struct Ctx final : CtxBase {
             CK(cudaMemcpyAsync(hS, S, head, cudaMemcpyDeviceToHost, stream));
             CK(cudaStreamSynchronize(stream));
         }
+        prev_iters = hS->iters;
         stats.cg_iters = hS->iters;
         stats.cg_rel_residual = std::sqrt(hS->rr / hS->bb);
         return 0;
@@ -713,7 +813,7 @@ void ink_default_params(ink_params* p) {
     p->gravity[0] = 0.f; p->gravity[1] = -0.1f; p->gravity[2] = 0.f;
     p->k_cfl = 0.2f; p->dt_min = 0.005f; p->dt_max = 1.f; p->buffer_size = 3;
     p->precision = 32; p->arith = INK_ARITH_STRICT; p->device = 0;
-    p->cg_rtol = 1e-6; p->cg_max_iters = 20000; p->cg_check_every = 16; p->cg_warm_start = 1; p->cg_precond = INK_PCG_NONE;
+    p->cg_rtol = 1e-6; p->cg_max_iters = 20000; p->cg_check_every = 16; p->cg_warm_start = 1; p->cg_precond = INK_PCG_MG;
     p->resort_interval = 16;
     p->rank = 0; p->world_size = 1;
 }

@@ -20,6 +20,7 @@ constexpr int kCgMaxBlocks = 148 * 8;
 
 struct CgScal {
     double rr, rr_old, dw, bb, tol2;
+    double rz, rz_old;   // <r, z> for preconditioned CG (z = B r); plain CG keeps rz == rr
     int iters, done;
     unsigned int ticket;
     int pad;
@@ -134,6 +135,7 @@ __global__ void __launch_bounds__(256) k_cg_init(Grid g, CgScal* S, const Real* 
             tot_bb = warp_sum(s);
             if (lane == 0) {
                 S->rr = tot_rr; S->rr_old = tot_rr; S->bb = tot_bb; S->dw = 0;
+                S->rz = tot_rr; S->rz_old = tot_rr;
                 S->iters = 0;
                 S->done = (tot_rr <= S->tol2 * tot_bb) ? 1 : 0;
             }
@@ -145,7 +147,7 @@ template <class Real, int V>
 __global__ void __launch_bounds__(256) k_cg_dir_matvec(Grid g, CgScal* S, const Real* __restrict__ r, const Real* __restrict__ d,
                                                        Real* __restrict__ dn, Real* __restrict__ w) {
     if (S->done) return;
-    const Real beta = (S->iters == 0) ? Real(0) : (Real)(S->rr / S->rr_old);
+    const Real beta = (S->iters == 0) ? Real(0) : (Real)(S->rz / S->rz_old);
     const int ZV = g.Z / V;
     const long long nvec = (long long)(g.j1 - g.j0) * g.X * ZV;
     double acc = 0;
@@ -186,11 +188,12 @@ __global__ void __launch_bounds__(256) k_cg_dir_matvec(Grid g, CgScal* S, const 
     }
 }
 
-template <class Real, int V>
+// PRECOND: z = B r is produced by the V-cycle that follows (mg.cuh), which also sets rz / rz_old
+template <class Real, int V, bool PRECOND>
 __global__ void __launch_bounds__(256) k_cg_update(Grid g, CgScal* S, Real* __restrict__ x, Real* __restrict__ r, const Real* __restrict__ d,
                                                    const Real* __restrict__ w) {
     if (S->done) return;
-    const Real alpha = (Real)(S->rr / S->dw);
+    const Real alpha = (Real)(S->rz / S->dw);
     const int ZV = g.Z / V;
     const long long nvec = (long long)(g.j1 - g.j0) * g.X * ZV;
     const long long base = (long long)g.j0 * g.sy;
@@ -213,6 +216,7 @@ __global__ void __launch_bounds__(256) k_cg_update(Grid g, CgScal* S, Real* __re
         if (threadIdx.x == 0) {
             S->rr_old = S->rr;
             S->rr = tot;
+            if (!PRECOND) { S->rz_old = S->rz; S->rz = tot; }
             S->iters += 1;
             if (tot <= S->tol2 * S->bb) S->done = 1;
         }
