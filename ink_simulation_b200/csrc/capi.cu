@@ -16,6 +16,7 @@
 #include "common.cuh"
 #include "grid_kernels.cuh"
 #include "mg.cuh"
+#include "mg_vec.cuh"
 #include "particle_kernels.cuh"
 
 namespace ink {
@@ -145,7 +146,7 @@ struct Ctx final : CtxBase {
     int init() override {
         const ink_params& p = P;
         if (p.X <= 0 || p.Y <= 0 || p.Z <= 0) { err = "grid dims must be positive"; return 2; }
-        if ((long long)p.X * p.Y * p.Z >= (1ll << 32)) { err = "grid too large for 32-bit cell keys"; return 2; }
+        if ((long long)p.X * p.Y * p.Z >= (1ll << 31)) { err = "grid too large for 32-bit cell indices"; return 2; }
         if (p.world_size != 1) { err = "multi-GPU contexts are created through ink_create with world_size > 1 (not built in this round)"; return 2; }
         CK(cudaSetDevice(p.device));
         cudaDeviceProp prop;
@@ -618,9 +619,19 @@ struct Ctx final : CtxBase {
     // z = B r : one V-cycle; the result is lv[0].xa; the last kernel also sets S->rz_old, S->rz = <r, z>
     int mg_vcycle(const Real* r0) {
         auto rhs = [&](int l) -> const Real* { return l == 0 ? r0 : lv[l].r; };
+        auto vblocks = [](const MgDims& d, int per) {   // one thread per `per` cells
+            const long long n = (long long)d.X * (d.j1 - d.j0) * (d.Z / per);
+            return (unsigned int)std::min<long long>(kMgBlocks, std::max<long long>(1, (n + 255) / 256));
+        };
         for (int l = 0; l < mg_lt; ++l) {
-            LAUNCH((k_mg_presmooth<Real>), mg_blocks(lv[l].d), 256, S, lv[l].d, lv[l].s, rhs(l), lv[l].xa);
-            LAUNCH((k_mg_residual_restrict<Real>), mg_blocks(lv[l + 1].d), 256, S, lv[l].d, lv[l + 1].d, lv[l].s, rhs(l), lv[l].xa, lv[l + 1].r);
+            const MgDims &df = lv[l].d, &dc = lv[l + 1].d;
+            if (df.Z % 4 == 0) {
+                LAUNCH((k_mg_presmooth_v4<Real>), vblocks(df, 4), 256, S, df, lv[l].s, rhs(l), lv[l].xa);
+                LAUNCH((k_mg_residual_restrict_v4<Real>), vblocks(dc, 2), 256, S, df, dc, lv[l].s, rhs(l), lv[l].xa, lv[l + 1].r);
+            } else {
+                LAUNCH((k_mg_presmooth<Real>), mg_blocks(df), 256, S, df, lv[l].s, rhs(l), lv[l].xa);
+                LAUNCH((k_mg_residual_restrict<Real>), mg_blocks(dc), 256, S, df, dc, lv[l].s, rhs(l), lv[l].xa, lv[l + 1].r);
+            }
         }
         {
             const MgDims& d = lv[mg_lt].d;
@@ -629,9 +640,16 @@ struct Ctx final : CtxBase {
             ++stats.kernel_launches;
         }
         for (int l = mg_lt - 1; l >= 0; --l) {
-            LAUNCH((k_mg_prolong_smooth<Real>), mg_blocks(lv[l].d), 256, S, lv[l].d, lv[l + 1].d, lv[l].s, rhs(l), lv[l].xa, lv[l + 1].xa, lv[l].xb);
-            if (l == 0) LAUNCH((k_mg_smooth<Real, true>), mg_blocks(lv[l].d), 256, S, lv[l].d, lv[l].s, rhs(l), lv[l].xb, lv[l].xa);
-            else LAUNCH((k_mg_smooth<Real, false>), mg_blocks(lv[l].d), 256, S, lv[l].d, lv[l].s, rhs(l), lv[l].xb, lv[l].xa);
+            const MgDims &df = lv[l].d, &dc = lv[l + 1].d;
+            if (df.Z % 4 == 0) {
+                LAUNCH((k_mg_prolong_smooth_v4<Real>), vblocks(df, 4), 256, S, df, dc, lv[l].s, rhs(l), lv[l].xa, lv[l + 1].xa, lv[l].xb);
+                if (l == 0) LAUNCH((k_mg_smooth_v4<Real, true>), vblocks(df, 4), 256, S, df, lv[l].s, rhs(l), lv[l].xb, lv[l].xa);
+                else LAUNCH((k_mg_smooth_v4<Real, false>), vblocks(df, 4), 256, S, df, lv[l].s, rhs(l), lv[l].xb, lv[l].xa);
+            } else {
+                LAUNCH((k_mg_prolong_smooth<Real>), mg_blocks(df), 256, S, df, dc, lv[l].s, rhs(l), lv[l].xa, lv[l + 1].xa, lv[l].xb);
+                if (l == 0) LAUNCH((k_mg_smooth<Real, true>), mg_blocks(df), 256, S, df, lv[l].s, rhs(l), lv[l].xb, lv[l].xa);
+                else LAUNCH((k_mg_smooth<Real, false>), mg_blocks(df), 256, S, df, lv[l].s, rhs(l), lv[l].xb, lv[l].xa);
+            }
         }
         CK(cudaGetLastError());
         return 0;

@@ -56,14 +56,35 @@ __device__ __forceinline__ Real mg_nbr_sum(const MgDims& d, const Real* __restri
     return a;
 }
 
-#define INK_MG_CELL_LOOP(d, tid, nth)                                                         \
-    for (long long t_ = (tid), rows_ = (long long)((d).j1 - (d).j0) * (d).X, tot_ = rows_ * (d).Z; t_ < tot_; t_ += (nth))
+// Strided cell iterator with INCREMENTAL (i, j, k) decode: two 32-bit divisions per thread at start, then adds and
+// compares per cell.  (Per-cell div/mod made the single-block tail issue-bound: 8 cells/thread x ~50 instructions.)
+struct MgIter {
+    unsigned int t, tot, nth;
+    int i, jl, k, di, dj, dk, X, Z;
+    __device__ __forceinline__ MgIter(const MgDims& d, unsigned int tid, unsigned int nthreads) {
+        X = d.X; Z = d.Z; nth = nthreads; t = tid;
+        tot = (unsigned int)(d.j1 - d.j0) * (unsigned int)d.X * (unsigned int)d.Z;
+        unsigned int row = tid / (unsigned int)Z;
+        k = (int)(tid - row * (unsigned int)Z);
+        jl = (int)(row / (unsigned int)X);
+        i = (int)(row - (unsigned int)jl * (unsigned int)X);
+        row = nthreads / (unsigned int)Z;
+        dk = (int)(nthreads - row * (unsigned int)Z);
+        dj = (int)(row / (unsigned int)X);
+        di = (int)(row - (unsigned int)dj * (unsigned int)X);
+    }
+    __device__ __forceinline__ bool ok() const { return t < tot; }
+    __device__ __forceinline__ void next() {
+        t += nth;
+        k += dk; if (k >= Z) { k -= Z; ++i; }
+        i += di; if (i >= X) { i -= X; ++jl; }
+        jl += dj;
+    }
+};
+#define INK_MG_CELL_LOOP(d, tid, nth) for (MgIter it_((d), (unsigned int)(tid), (unsigned int)(nth)); it_.ok(); it_.next())
 
-#define INK_MG_DECODE(d)                                  \
-    const int k = (int)(t_ % (d).Z);                      \
-    const long long row_ = t_ / (d).Z;                    \
-    const int i = (int)(row_ % (d).X);                    \
-    const int j = (d).j0 + (int)(row_ / (d).X);           \
+#define INK_MG_DECODE(d)                                   \
+    const int i = it_.i, k = it_.k, j = (d).j0 + it_.jl;   \
     const long long c = mg_idx((d), i, j, k);
 
 // two Jacobi sweeps from a zero guess, fused: x = c (2 r - (omega/6) L r)

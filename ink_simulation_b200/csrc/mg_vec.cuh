@@ -1,0 +1,174 @@
+// mg_vec.cuh — 128-bit vectorised versions of the global-memory multigrid kernels of mg.cuh for levels whose z extent
+// is a multiple of 4 (every BASELINE grid on its fine levels).  One thread owns 4 consecutive z cells of one (i,j)
+// row: the (i,j,k) decode is amortised over 4 cells and every row access is one LDG.128 / STG.128.  Arithmetic is
+// identical to the scalar device functions (same expressions per cell), so scalar and vector levels can be mixed.
+#pragma once
+#include "mg.cuh"
+
+namespace ink {
+
+template <class Real>
+using P4 = Pack<Real, 4>;
+
+template <class Real>
+__device__ __forceinline__ P4<Real> p4_zero() { P4<Real> z; z.a[0] = z.a[1] = z.a[2] = z.a[3] = Real(0); return z; }
+
+// thread -> (i, j, k = 4*kv, c) of a level; returns false past the end
+__device__ __forceinline__ bool mg_vec_cell(const MgDims& d, unsigned int t, int& i, int& j, int& k, long long& c) {
+    const unsigned int ZV = (unsigned int)d.Z >> 2;
+    const unsigned int tot = (unsigned int)(d.j1 - d.j0) * (unsigned int)d.X * ZV;
+    if (t >= tot) return false;
+    const unsigned int row = t / ZV;
+    k = (int)(t - row * ZV) << 2;
+    const unsigned int jl = row / (unsigned int)d.X;
+    i = (int)(row - jl * (unsigned int)d.X);
+    j = d.j0 + (int)jl;
+    c = mg_idx(d, i, j, k);
+    return true;
+}
+
+// 6 x - (in-grid, in-slab neighbours) for the 4 cells at c; xc = the centre pack (already loaded)
+template <class Real>
+__device__ __forceinline__ void mg_lap4(const MgDims& d, const Real* __restrict__ x, const P4<Real>& xc, int i, int j, int k, long long c, Real (&L)[4]) {
+    const long long sx = d.Z, sy = (long long)d.X * d.Z;
+    Real nb[4] = {Real(0), Real(0), Real(0), Real(0)};
+#define INK_ROW(cond, off)                                         \
+    if (cond) {                                                    \
+        const P4<Real> q = ldp<Real, 4>(x + c + (off));            \
+        nb[0] += q.a[0]; nb[1] += q.a[1]; nb[2] += q.a[2]; nb[3] += q.a[3]; \
+    }
+    INK_ROW(i + 1 < d.X, sx)
+    INK_ROW(i > 0, -sx)
+    INK_ROW(j + 1 < d.j1, sy)
+    INK_ROW(j > d.j0, -sy)
+#undef INK_ROW
+    const Real zl = (k > 0) ? x[c - 1] : Real(0);
+    const Real zr = (k + 4 < d.Z) ? x[c + 4] : Real(0);
+    L[0] = Real(6) * xc.a[0] - (nb[0] + zl + xc.a[1]);
+    L[1] = Real(6) * xc.a[1] - (nb[1] + xc.a[0] + xc.a[2]);
+    L[2] = Real(6) * xc.a[2] - (nb[2] + xc.a[1] + xc.a[3]);
+    L[3] = Real(6) * xc.a[3] - (nb[3] + xc.a[2] + zr);
+}
+
+template <class Real>
+__global__ void __launch_bounds__(256) k_mg_presmooth_v4(const CgScal* S, MgDims d, Real s, const Real* __restrict__ r, Real* __restrict__ x) {
+    if (S->done) return;
+    const Real cj = Real(kMgOmega) / (Real(6) * s), w6 = Real(kMgOmega) / Real(6);
+    int i, j, k; long long c;
+    for (unsigned int t = blockIdx.x * blockDim.x + threadIdx.x; mg_vec_cell(d, t, i, j, k, c); t += gridDim.x * blockDim.x) {
+        const P4<Real> rc = ldp<Real, 4>(r + c);
+        Real L[4];
+        mg_lap4<Real>(d, r, rc, i, j, k, c, L);
+        P4<Real> o;
+#pragma unroll
+        for (int a = 0; a < 4; ++a) o.a[a] = cj * (Real(2) * rc.a[a] - w6 * L[a]);
+        stp<Real, 4>(x + c, o);
+    }
+}
+
+template <class Real, bool FINAL>
+__global__ void __launch_bounds__(256) k_mg_smooth_v4(CgScal* S, MgDims d, Real s, const Real* __restrict__ r, const Real* __restrict__ xi, Real* __restrict__ xo) {
+    if (S->done) return;
+    const Real cj = Real(kMgOmega) / (Real(6) * s);
+    int i, j, k; long long c;
+    double acc = 0;
+    for (unsigned int t = blockIdx.x * blockDim.x + threadIdx.x; mg_vec_cell(d, t, i, j, k, c); t += gridDim.x * blockDim.x) {
+        const P4<Real> xc = ldp<Real, 4>(xi + c), rc = ldp<Real, 4>(r + c);
+        Real L[4];
+        mg_lap4<Real>(d, xi, xc, i, j, k, c, L);
+        P4<Real> o;
+#pragma unroll
+        for (int a = 0; a < 4; ++a) {
+            o.a[a] = xc.a[a] + cj * (rc.a[a] - s * L[a]);
+            acc += (double)rc.a[a] * (double)o.a[a];
+        }
+        stp<Real, 4>(xo + c, o);
+    }
+    if (FINAL) {
+        double tot;
+        if (block_sum_last(acc, S, 0, tot)) {
+            if (threadIdx.x == 0) { S->rz_old = S->rz; S->rz = tot; }
+        }
+    }
+}
+
+// x' = xi + P e ; xo = x' + c (r - s L x').  The 4 cells k..k+3 (k % 4 == 0) have parents K = k/2, k/2 + 1.
+template <class Real>
+__global__ void __launch_bounds__(256) k_mg_prolong_smooth_v4(const CgScal* S, MgDims df, MgDims dc, Real s, const Real* __restrict__ r,
+                                                              const Real* __restrict__ xi, const Real* __restrict__ e, Real* __restrict__ xo) {
+    if (S->done) return;
+    const Real cj = Real(kMgOmega) / (Real(6) * s);
+    const long long sx = df.Z, sy = (long long)df.X * df.Z;
+    int i, j, k; long long c;
+    for (unsigned int t = blockIdx.x * blockDim.x + threadIdx.x; mg_vec_cell(df, t, i, j, k, c); t += gridDim.x * blockDim.x) {
+        const int K = k >> 1;
+        // x' of one fine row (ii, jj): xi row pack + the two parent values of coarse row (ii>>1, jj>>1)
+        auto row = [&](int ii, int jj, long long off) -> P4<Real> {
+            P4<Real> q = ldp<Real, 4>(xi + c + off);
+            const Real* er = e + mg_idx(dc, ii >> 1, jj >> 1, K);
+            const Real e0 = er[0], e1 = (K + 1 < dc.Z) ? er[1] : Real(0);   // Z % 4 == 0 => K + 1 < dc.Z always; guard is free
+            q.a[0] += e0; q.a[1] += e0; q.a[2] += e1; q.a[3] += e1;
+            return q;
+        };
+        const P4<Real> xc = row(i, j, 0);
+        Real nb[4] = {Real(0), Real(0), Real(0), Real(0)};
+#define INK_ROW(cond, ii, jj, off)                                                   \
+        if (cond) {                                                                  \
+            const P4<Real> q = row(ii, jj, off);                                     \
+            nb[0] += q.a[0]; nb[1] += q.a[1]; nb[2] += q.a[2]; nb[3] += q.a[3];      \
+        }
+        INK_ROW(i + 1 < df.X, i + 1, j, sx)
+        INK_ROW(i > 0, i - 1, j, -sx)
+        INK_ROW(j + 1 < df.j1, i, j + 1, sy)
+        INK_ROW(j > df.j0, i, j - 1, -sy)
+#undef INK_ROW
+        const long long ec = mg_idx(dc, i >> 1, j >> 1, K);
+        const Real zl = (k > 0) ? xi[c - 1] + e[ec - 1] : Real(0);
+        const Real zr = (k + 4 < df.Z) ? xi[c + 4] + e[ec + 2] : Real(0);
+        const P4<Real> rc = ldp<Real, 4>(r + c);
+        P4<Real> o;
+        o.a[0] = xc.a[0] + cj * (rc.a[0] - s * (Real(6) * xc.a[0] - (nb[0] + zl + xc.a[1])));
+        o.a[1] = xc.a[1] + cj * (rc.a[1] - s * (Real(6) * xc.a[1] - (nb[1] + xc.a[0] + xc.a[2])));
+        o.a[2] = xc.a[2] + cj * (rc.a[2] - s * (Real(6) * xc.a[2] - (nb[2] + xc.a[1] + xc.a[3])));
+        o.a[3] = xc.a[3] + cj * (rc.a[3] - s * (Real(6) * xc.a[3] - (nb[3] + xc.a[2] + zr)));
+        stp<Real, 4>(xo + c, o);
+    }
+}
+
+// r_c = P^T (r - s L x): one thread produces the two coarse cells (I, J, K..K+1), K even, from the 4 fine rows
+// (2I+a, 2J+b) x cells 2K..2K+3.
+template <class Real>
+__global__ void __launch_bounds__(256) k_mg_residual_restrict_v4(const CgScal* S, MgDims df, MgDims dc, Real s, const Real* __restrict__ r,
+                                                                 const Real* __restrict__ x, Real* __restrict__ rc) {
+    if (S->done) return;
+    const unsigned int ZV = (unsigned int)dc.Z >> 1;   // df.Z % 4 == 0  =>  dc.Z even
+    const unsigned int tot = (unsigned int)(dc.j1 - dc.j0) * (unsigned int)dc.X * ZV;
+    for (unsigned int t = blockIdx.x * blockDim.x + threadIdx.x; t < tot; t += gridDim.x * blockDim.x) {
+        const unsigned int rowc = t / ZV;
+        const int K = (int)(t - rowc * ZV) << 1;
+        const unsigned int jl = rowc / (unsigned int)dc.X;
+        const int I = (int)(rowc - jl * (unsigned int)dc.X), J = dc.j0 + (int)jl;
+        Real acc0 = Real(0), acc1 = Real(0);
+#pragma unroll
+        for (int b = 0; b < 2; ++b) {
+            const int fj = 2 * J + b;
+            if (fj >= df.j1 || fj < df.j0) continue;
+#pragma unroll
+            for (int a = 0; a < 2; ++a) {
+                const int fi = 2 * I + a;
+                if (fi >= df.X) continue;
+                const int fk = 2 * K;
+                const long long f = mg_idx(df, fi, fj, fk);
+                const P4<Real> xc = ldp<Real, 4>(x + f), rr = ldp<Real, 4>(r + f);
+                Real L[4];
+                mg_lap4<Real>(df, x, xc, fi, fj, fk, f, L);
+                acc0 += (rr.a[0] - s * L[0]) + (rr.a[1] - s * L[1]);
+                acc1 += (rr.a[2] - s * L[2]) + (rr.a[3] - s * L[3]);
+            }
+        }
+        Pack<Real, 2> o; o.a[0] = acc0; o.a[1] = acc1;
+        stp<Real, 2>(rc + mg_idx(dc, I, J, K), o);
+    }
+}
+
+}  // namespace ink
