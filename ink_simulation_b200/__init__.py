@@ -6,4 +6,4 @@ Layout:  csrc/  CUDA kernels + the C ABI (include/ink_capi.h -> libinkb200.so)
          system.py / inksim.py  Python mirror of the same interface for tests and bench.py
 """
 from ._capi import LIB_PATH, load  # noqa: F401
-from .system import InkError, Params, System  # noqa: F401
+from .system import InkError, Params, System, create_distributed, nccl_unique_id, shard_range, slab_range  # noqa: F401

@@ -17,6 +17,7 @@
 #include "grid_kernels.cuh"
 #include "mg.cuh"
 #include "mg_vec.cuh"
+#include "nccl_shim.h"
 #include "particle_kernels.cuh"
 
 namespace ink {
@@ -31,6 +32,17 @@ static thread_local std::string g_create_error;
             snprintf(buf_, sizeof buf_, "%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
             this->err = buf_;                                                                            \
             return 1;                                                                                    \
+        }                                                                                                \
+    } while (0)
+
+#define NK(call)                                                                                         \
+    do {                                                                                                 \
+        ncclResult_t r_ = (call);                                                                        \
+        if (r_ != ncclSuccess) {                                                                         \
+            char buf_[512];                                                                              \
+            snprintf(buf_, sizeof buf_, "%s:%d %s -> %s", __FILE__, __LINE__, #call, nccl().GetErrorString(r_)); \
+            this->err = buf_;                                                                            \
+            return 4;                                                                                    \
         }                                                                                                \
     } while (0)
 
@@ -78,8 +90,13 @@ struct CtxBase {
 
 template <class Real>
 struct Ctx final : CtxBase {
-    Grid g{};
+    Grid g{};          // g.j0 / g.j1 = the y-slab of rows this rank owns (whole grid on one GPU)
     Consts<Real> C{};
+    // multi-GPU (one process per GPU): NCCL communicator over NVLink; every rank keeps FULL-size grid arrays, owns
+    // rows [g.j0, g.j1) and a contiguous index shard of every particle drop
+    ncclComm_t comm = nullptr;
+    int rank = 0, world = 1;
+    std::vector<int> slab_lo;   // slab_lo[r] .. slab_lo[r+1] = rows of rank r
     // MAC grid state (struct Cell, src/system.h:41-50) as SoA; vel[cur] is the committed (old == curr) field
     Real* vel[2][3] = {{nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr}};
     int cur = 0;
@@ -99,7 +116,7 @@ struct Ctx final : CtxBase {
     uint8_t *seed = nullptr, *mark = nullptr;
     unsigned int* d_scal = nullptr;  // [0] max speed bits, [1] oob particle count
     unsigned int* h_scal = nullptr;  // pinned
-    bool maxv_valid = false, seed_valid = false;
+    bool maxv_valid = false, seed_valid = false, seed_global = false;
     // phantom map cells created by out-of-grid particles (Q8): all carry the same accumulated dt*g
     bool have_phantom = false, oob_now = false;
     Real phantom_v[3] = {0, 0, 0};
@@ -119,6 +136,7 @@ struct Ctx final : CtxBase {
     bool ev_valid = false;
 
     ~Ctx() override {
+        if (comm) nccl().CommDestroy(comm);
         for (auto& b : vel)
             for (auto& p : b) cudaFree(p);
         for (auto& p : curl) cudaFree(p);
@@ -147,14 +165,26 @@ struct Ctx final : CtxBase {
         const ink_params& p = P;
         if (p.X <= 0 || p.Y <= 0 || p.Z <= 0) { err = "grid dims must be positive"; return 2; }
         if ((long long)p.X * p.Y * p.Z >= (1ll << 31)) { err = "grid too large for 32-bit cell indices"; return 2; }
-        if (p.world_size != 1) { err = "multi-GPU contexts are created through ink_create with world_size > 1 (not built in this round)"; return 2; }
+        if (p.world_size < 1 || p.rank < 0 || p.rank >= p.world_size) { err = "bad rank / world_size"; return 2; }
+        rank = p.rank; world = p.world_size;
+        slab_lo.resize(world + 1);
+        for (int r = 0; r <= world; ++r) slab_lo[r] = (int)((long long)p.Y * r / world);
+        if (world > 1 && p.Y / world < 4) { err = "y-slab decomposition needs at least 4 grid rows per rank"; return 2; }
         CK(cudaSetDevice(p.device));
         cudaDeviceProp prop;
         CK(cudaGetDeviceProperties(&prop, p.device));
         if (prop.major < 10) { err = "libinkb200 is built for sm_100a (B200) only"; return 3; }
         g.X = p.X; g.Y = p.Y; g.Z = p.Z;
         g.sx = p.Z; g.sy = (long long)p.X * p.Z; g.n = (long long)p.X * p.Y * p.Z;
-        g.j0 = 0; g.j1 = p.Y;
+        g.j0 = slab_lo[rank]; g.j1 = slab_lo[rank + 1];
+        if (world > 1) {
+            const std::string e = nccl().load();
+            if (!e.empty()) { err = e; return 4; }
+            ncclUniqueId id;
+            static_assert(sizeof(id) <= sizeof(p.nccl_id), "ncclUniqueId does not fit ink_params::nccl_id");
+            memcpy(&id, p.nccl_id, sizeof id);
+            NK(nccl().CommInitRank(&comm, world, id, rank));
+        }
         // constants converted the way the reference's expressions convert them (float first, then Real)
         C.h = (Real)p.cell_dim;
         C.bx = (Real)(float)(p.X * p.cell_dim); C.by = (Real)(float)(p.Y * p.cell_dim); C.bz = (Real)(float)(p.Z * p.cell_dim);
@@ -170,6 +200,7 @@ struct Ctx final : CtxBase {
         for (auto& ptr : curl) { CK(cudaMalloc(&ptr, nb)); CK(cudaMemsetAsync(ptr, 0, nb, stream)); }
         for (Real** ptr : {&pres, &q, &rhs, &cg_r, &cg_d[0], &cg_d[1], &cg_w}) { CK(cudaMalloc(ptr, nb)); CK(cudaMemsetAsync(*ptr, 0, nb, stream)); }
         CK(cudaMalloc(&S, sizeof(CgScal))); CK(cudaMemsetAsync(S, 0, sizeof(CgScal), stream));
+        { const int dist = world > 1; CK(cudaMemcpyAsync(&S->dist, &dist, sizeof(int), cudaMemcpyHostToDevice, stream)); }
         CK(cudaMallocHost(&hS, sizeof(CgScal)));
         CK(cudaMalloc(&seed, g.n)); CK(cudaMemsetAsync(seed, 0, g.n, stream));
         CK(cudaMalloc(&mark, g.n)); CK(cudaMemsetAsync(mark, 0, g.n, stream));
@@ -218,6 +249,53 @@ struct Ctx final : CtxBase {
     Real* U(int a) { return vel[cur][a]; }
     Real* Un(int a) { return vel[cur ^ 1][a]; }
     unsigned int cell_blocks() const { return nblk((long long)(g.j1 - g.j0) * g.sy); }
+    static unsigned int cell_blocks(const Grid& q) { return nblk((long long)(q.j1 - q.j0) * q.sy); }
+    // this rank's slab widened by `ext` rows each side (clipped to the grid): phases before a stencil phase are computed
+    // redundantly on the rows the stencil will read, so the velocity phases need NO halo exchange (multi-GPU)
+    Grid slab(int ext) const {
+        Grid q = g;
+        if (world > 1) { q.j0 = std::max(0, g.j0 - ext); q.j1 = std::min(g.Y, g.j1 + ext); }
+        return q;
+    }
+    static ncclDataType_t nc_real() { return sizeof(Real) == 4 ? ncclFloat : ncclDouble; }
+    // rows [j0-nlo, j0) <- rank-1's top rows, rows [j1, j1+nhi) <- rank+1's bottom rows (array indexed like the grid)
+    int halo_exchange(Real* a, int nlo, int nhi) {
+        if (world == 1) return 0;
+        const size_t row = (size_t)g.sy;
+        NK(nccl().GroupStart());
+        if (rank > 0) {
+            if (nlo) NK(nccl().Recv(a + (size_t)(g.j0 - nlo) * row, nlo * row, nc_real(), rank - 1, comm, stream));
+            if (nhi) NK(nccl().Send(a + (size_t)g.j0 * row, nhi * row, nc_real(), rank - 1, comm, stream));
+        }
+        if (rank + 1 < world) {
+            if (nhi) NK(nccl().Recv(a + (size_t)g.j1 * row, nhi * row, nc_real(), rank + 1, comm, stream));
+            if (nlo) NK(nccl().Send(a + (size_t)(g.j1 - nlo) * row, nlo * row, nc_real(), rank + 1, comm, stream));
+        }
+        NK(nccl().GroupEnd());
+        return 0;
+    }
+    // every rank's own rows -> every rank (in place): one broadcast per owner inside a group
+    int allgather_rows(void* a, size_t elem) {
+        if (world == 1) return 0;
+        const size_t row = (size_t)g.sy * elem;
+        NK(nccl().GroupStart());
+        for (int r = 0; r < world; ++r) {
+            char* ptr = (char*)a + (size_t)slab_lo[r] * row;
+            NK(nccl().Broadcast(ptr, ptr, (size_t)(slab_lo[r + 1] - slab_lo[r]) * row, ncclChar, r, comm, stream));
+        }
+        NK(nccl().GroupEnd());
+        return 0;
+    }
+    int allgather_velocity() {
+        for (int a = 0; a < 3; ++a)
+            if (int rc = allgather_rows(U(a), sizeof(Real))) return rc;
+        return 0;
+    }
+    int allreduce(void* buf, size_t count, ncclDataType_t t, ncclRedOp_t op) {
+        if (world == 1) return 0;
+        NK(nccl().AllReduce(buf, buf, count, t, op, comm, stream));
+        return 0;
+    }
     bool vec4() const { return (g.Z % 4) == 0; }
     unsigned int cg_blocks() const {
         const long long nvec = (long long)(g.j1 - g.j0) * g.X * (g.Z / (vec4() ? 4 : 1));
@@ -294,6 +372,13 @@ struct Ctx final : CtxBase {
     int set_particles(int drop, const void* pos, const void* vel_, int64_t n, int hd) override {
         if (int rc = check_hd(hd, err)) return rc;
         if (drop < 0 || n < 0) { err = "bad drop / n"; return 2; }
+        if (world > 1) {   // every rank is handed the full drop and keeps the contiguous index shard [n*r/W, n*(r+1)/W)
+            const long long first = (long long)n * rank / world, last = (long long)n * (rank + 1) / world;
+            const size_t es0 = hd == 64 ? 8 : 4;
+            pos = (const char*)pos + (size_t)first * 3 * es0;
+            if (vel_) vel_ = (const char*)vel_ + (size_t)first * 3 * es0;
+            n = last - first;
+        }
         if (drop > (int)drop_n.size()) { err = "drops must be added in order (0, 1, ...)"; return 2; }
         // rebuild the concatenation in caller order: un-bin what we have, replace / append this drop
         std::vector<long long> new_n = drop_n;
@@ -388,11 +473,20 @@ struct Ctx final : CtxBase {
         return 0;
     }
     int ensure_seed() {
-        if (seed_valid) return 0;
+        if (seed_valid) {
+            if (world > 1 && !seed_global) {
+                if (int rc = allreduce(seed, (size_t)g.n, ncclUint8, ncclMax)) return rc;
+                seed_global = true;
+            }
+            return 0;
+        }
         CK(cudaMemsetAsync(seed, 0, g.n, stream));
         CK(cudaMemsetAsync(d_scal + 1, 0, sizeof(unsigned int), stream));
         if (np > 0) LAUNCH((k_mark_particle_cells<Real>), nblk(np), 256, g, np, part[pcur], seed, d_scal + 1);
         CK(cudaGetLastError());
+        if (int rc = allreduce(d_scal + 1, 1, ncclUint32, ncclSum)) return rc;
+        if (int rc = allreduce(seed, (size_t)g.n, ncclUint8, ncclMax)) return rc;   // OR of every rank's particle cells
+        seed_global = true;
         CK(cudaMemcpyAsync(h_scal + 1, d_scal + 1, sizeof(unsigned int), cudaMemcpyDeviceToHost, stream));
         CK(cudaStreamSynchronize(stream));
         oob_now = h_scal[1] > 0;
@@ -420,8 +514,9 @@ struct Ctx final : CtxBase {
         }
         return 0;
     }
-    int get_pressure(void* p, int hd) override {
+    int get_pressure(void* p, int hd) override {   // multi-GPU: collective (every rank calls it)
         if (int rc = check_hd(hd, err)) return rc;
+        if (int rc = allgather_rows(pres, sizeof(Real))) return rc;
         return grid_out_any(pres, p, hd);
     }
     int set_pressure(const void* p, int hd) override {
@@ -435,6 +530,7 @@ struct Ctx final : CtxBase {
     int get_mark(uint8_t* m) override {
         if (int rc = need_stage((size_t)g.n * 8)) return rc;
         uint8_t* dst = is_device_ptr(m) ? m : (uint8_t*)stage;
+        if (int rc = allgather_rows(mark, 1)) return rc;
         LAUNCH(k_mark_to_xyz, nblk(g.n), 256, g, mark, dst);
         CK(cudaGetLastError());
         if (dst != m) CK(cudaMemcpyAsync(m, dst, g.n, cudaMemcpyDeviceToHost, stream));
@@ -445,6 +541,7 @@ struct Ctx final : CtxBase {
         if (int rc = check_hd(hd, err)) return rc;
         LAUNCH((k_divergence<Real>), cell_blocks(), 256, g, 0, Real(0), Real(0), U(0), U(1), U(2), rhs);
         CK(cudaGetLastError());
+        if (int rc = allgather_rows(rhs, sizeof(Real))) return rc;
         return grid_out_any(rhs, d, hd);
     }
     int sample_velocity(const void* pos, int64_t n, void* out, int hd) override {
@@ -481,6 +578,7 @@ struct Ctx final : CtxBase {
             const unsigned int b = std::min<unsigned int>(cell_blocks(), kSMs * 8);
             LAUNCH((k_max_speed<Real>), b, 256, g, U(0), U(1), U(2), d_scal);
             CK(cudaGetLastError());
+            if (int rc = allreduce(d_scal, 1, ncclUint32, ncclMax)) return rc;   // non-negative floats order like their bits
             maxv_valid = true;
         }
         CK(cudaMemcpyAsync(h_scal, d_scal, sizeof(unsigned int), cudaMemcpyDeviceToHost, stream));
@@ -515,7 +613,7 @@ struct Ctx final : CtxBase {
     }
     void swap_vel() { cur ^= 1; }
 
-    int advect_impl(Real dt, bool allow_skip) {
+    int advect_impl(Real dt, bool allow_skip, int ext = 0) {
         stats.advect_skipped = 0;
         if (allow_skip) {
             // With CFL-limited dt the back-traced cell centre cannot leave its cell, so the nearest-cell copy is the
@@ -525,34 +623,43 @@ struct Ctx final : CtxBase {
             const double h = P.cell_dim, margin = std::min(0.5 * h, 1.0 - 0.5 * h);
             if (margin > 0 && std::isfinite(mv) && std::fabs((double)dt) * (double)mv <= 0.9 * margin) { stats.advect_skipped = 1; return 0; }
         }
-        LAUNCH((k_advect<Real>), cell_blocks(), 256, g, C, dt, U(0), U(1), U(2), Un(0), Un(1), Un(2));
+        { const Grid q = slab(ext); LAUNCH((k_advect<Real>), cell_blocks(q), 256, q, C, dt, U(0), U(1), U(2), Un(0), Un(1), Un(2)); }
         CK(cudaGetLastError());
         swap_vel();
         maxv_valid = false;
         return 0;
     }
-    int advect(double dt) override { return advect_impl((Real)(float)dt, true); }
+    int advect(double dt) override {
+        if (int rc = advect_impl((Real)(float)dt, true)) return rc;
+        return stats.advect_skipped ? 0 : allgather_velocity();
+    }
 
-    int forces_impl(Real dt) {
+    int forces_impl(Real dt, int ext = 0) {
         if (int rc = ensure_seed()) return rc;
         const Real gx = dt * C.g[0], gy = dt * C.g[1], gz = dt * C.g[2];
-        LAUNCH((k_dilate_add_gravity<Real>), cell_blocks(), 256, g, C.R, seed, mark, gx, gy, gz, U(0), U(1), U(2));
+        { const Grid q = slab(ext); LAUNCH((k_dilate_add_gravity<Real>), cell_blocks(q), 256, q, C.R, seed, mark, gx, gy, gz, U(0), U(1), U(2)); }
         CK(cudaGetLastError());
         if (oob_now) { phantom_v[0] += gx; phantom_v[1] += gy; phantom_v[2] += gz; }
         maxv_valid = false;
         return 0;
     }
-    int forces(double dt) override { return forces_impl((Real)(float)dt); }
+    int forces(double dt) override {
+        if (int rc = forces_impl((Real)(float)dt)) return rc;
+        return allgather_velocity();
+    }
 
-    int viscosity_impl(Real dt) {
+    int viscosity_impl(Real dt, int ext = 0) {
         const Real s = dt * C.visc;
-        LAUNCH((k_viscosity<Real>), cell_blocks(), 256, g, s, U(0), U(1), U(2), Un(0), Un(1), Un(2));
+        { const Grid q = slab(ext); LAUNCH((k_viscosity<Real>), cell_blocks(q), 256, q, s, U(0), U(1), U(2), Un(0), Un(1), Un(2)); }
         CK(cudaGetLastError());
         swap_vel();
         maxv_valid = false;
         return 0;
     }
-    int viscosity(double dt) override { return viscosity_impl((Real)(float)dt); }
+    int viscosity(double dt) override {
+        if (int rc = viscosity_impl((Real)(float)dt)) return rc;
+        return allgather_velocity();
+    }
 
     int pressure_rhs(double dt_, void* b, int hd) override {
         if (int rc = check_hd(hd, err)) return rc;
@@ -560,6 +667,7 @@ struct Ctx final : CtxBase {
         const Real scale = (C.rho * C.h) / dt;
         LAUNCH((k_divergence<Real>), cell_blocks(), 256, g, 1, scale, C.patm, U(0), U(1), U(2), rhs);
         CK(cudaGetLastError());
+        if (int rc = allgather_rows(rhs, sizeof(Real))) return rc;
         return grid_out_any(rhs, b, hd);
     }
 
@@ -655,14 +763,28 @@ struct Ctx final : CtxBase {
         return 0;
     }
 
-    // solve M x = f (M = -A) by (preconditioned) CG; x holds the initial guess
+    // solve M x = f (M = -A) by (preconditioned) CG; x holds the initial guess.
+    // Multi-GPU: every rank iterates on its own rows; per iteration 2 all-reduces (<d,w>; <r,r> & <r,z> together) and one
+    // boundary-row exchange of z.  The preconditioner is slab-local (no traffic).
+    int cg_post(int stage) {
+        k_cg_post<<<1, 32, 0, stream>>>(S, stage, use_mg ? 1 : 0);
+        ++stats.kernel_launches;
+        return 0;
+    }
     int cg_solve(const Real* f, Real* x) {
         const unsigned int nb = cg_blocks();
+        const bool dist = world > 1;
+        const int hlo = (dist && rank > 0) ? 1 : 0, hhi = (dist && rank + 1 < world) ? 1 : 0;
         const double tol2 = P.cg_rtol * P.cg_rtol;
         CK(cudaMemcpyAsync(&S->tol2, &tol2, sizeof(double), cudaMemcpyHostToDevice, stream));
+        if (int rc = halo_exchange(x, 1, 1)) return rc;     // warm start: the initial residual needs x on the neighbour rows
         if (vec4()) LAUNCH((k_cg_init<Real, 4>), nb, 256, g, S, f, x, cg_r);
         else LAUNCH((k_cg_init<Real, 1>), nb, 256, g, S, f, x, cg_r);
         CK(cudaGetLastError());
+        if (dist) {
+            if (int rc = allreduce(S->loc, 4, ncclDouble, ncclSum)) return rc;
+            cg_post(0);
+        }
         const size_t head = offsetof(CgScal, partial);
         CK(cudaMemcpyAsync(hS, S, head, cudaMemcpyDeviceToHost, stream));
         CK(cudaStreamSynchronize(stream));
@@ -672,11 +794,16 @@ struct Ctx final : CtxBase {
             return 0;
         }
         int dcur = 0, launched = 0;
-        const Real* zsrc = cg_r;
+        Real* zsrc = cg_r;
         if (use_mg) {
             if (int rc = mg_vcycle(cg_r)) return rc;
             zsrc = lv[0].xa;
+            if (dist) {
+                if (int rc = allreduce(S->loc + 2, 1, ncclDouble, ncclSum)) return rc;
+                cg_post(3);
+            }
         }
+        if (int rc = halo_exchange(zsrc, 1, 1)) return rc;
         // host polls convergence every `every` iterations; kernels launched after convergence are no-ops (S->done).
         // With the preconditioner the count is small and steady from step to step: launch last solve's count first.
         const int every = use_mg ? 2 : std::max(1, P.cg_check_every);
@@ -684,17 +811,26 @@ struct Ctx final : CtxBase {
             int batch = std::min(every, P.cg_max_iters - launched);
             if (use_mg && launched == 0 && prev_iters > 1) batch = std::min(prev_iters, P.cg_max_iters);
             for (int it = 0; it < batch; ++it) {
+                if (vec4()) LAUNCH((k_cg_dir_matvec<Real, 4>), nb, 256, g, S, zsrc, cg_d[dcur], cg_d[dcur ^ 1], cg_w, hlo, hhi);
+                else LAUNCH((k_cg_dir_matvec<Real, 1>), nb, 256, g, S, zsrc, cg_d[dcur], cg_d[dcur ^ 1], cg_w, hlo, hhi);
+                if (dist) {
+                    if (int rc = allreduce(S->loc, 1, ncclDouble, ncclSum)) return rc;
+                    cg_post(1);
+                }
                 if (vec4()) {
-                    LAUNCH((k_cg_dir_matvec<Real, 4>), nb, 256, g, S, zsrc, cg_d[dcur], cg_d[dcur ^ 1], cg_w);
                     if (use_mg) LAUNCH((k_cg_update<Real, 4, true>), nb, 256, g, S, x, cg_r, cg_d[dcur ^ 1], cg_w);
                     else LAUNCH((k_cg_update<Real, 4, false>), nb, 256, g, S, x, cg_r, cg_d[dcur ^ 1], cg_w);
                 } else {
-                    LAUNCH((k_cg_dir_matvec<Real, 1>), nb, 256, g, S, zsrc, cg_d[dcur], cg_d[dcur ^ 1], cg_w);
                     if (use_mg) LAUNCH((k_cg_update<Real, 1, true>), nb, 256, g, S, x, cg_r, cg_d[dcur ^ 1], cg_w);
                     else LAUNCH((k_cg_update<Real, 1, false>), nb, 256, g, S, x, cg_r, cg_d[dcur ^ 1], cg_w);
                 }
                 if (use_mg)
                     if (int rc = mg_vcycle(cg_r)) return rc;
+                if (dist) {
+                    if (int rc = allreduce(S->loc + 1, 2, ncclDouble, ncclSum)) return rc;
+                    cg_post(2);
+                    if (int rc = halo_exchange(zsrc, 1, 1)) return rc;
+                }
                 dcur ^= 1;
             }
             launched += batch;
@@ -708,26 +844,35 @@ struct Ctx final : CtxBase {
         return 0;
     }
 
-    int grad_subtract(Real dt) {
+    int grad_subtract(Real dt, int ext = 0) {
         const Real s = dt / (C.rho * C.h);
-        LAUNCH((k_grad_subtract<Real>), cell_blocks(), 256, g, s, pres, U(0), U(1), U(2));
+        { const Grid q = slab(ext); LAUNCH((k_grad_subtract<Real>), cell_blocks(q), 256, q, s, pres, U(0), U(1), U(2)); }
         CK(cudaGetLastError());
         maxv_valid = false;
         return 0;
     }
-    int pressure_impl(Real dt) {
+    // ext = rows of redundancy the caller needs on the projected velocity (viscosity must have produced ext + 0 rows;
+    // the pressure is exchanged ext + 1 rows down / ext rows up after the solve)
+    int pressure_impl(Real dt, int ext = 0) {
         const Real scale = (C.rho * C.h) / dt;
         LAUNCH((k_divergence<Real>), cell_blocks(), 256, g, 2, scale, C.patm, U(0), U(1), U(2), rhs);
         CK(cudaGetLastError());
         if (!(P.cg_warm_start && have_q)) CK(cudaMemsetAsync(q, 0, (size_t)g.n * sizeof(Real), stream));
         if (int rc = cg_solve(rhs, q)) return rc;
         have_q = true;
+        if (int rc = halo_exchange(q, ext + 1, ext)) return rc;
         LAUNCH((k_add_scalar<Real>), nblk(g.n), 256, g.n, C.patm, q, pres);
         CK(cudaGetLastError());
-        return grad_subtract(dt);
+        return grad_subtract(dt, ext);
     }
-    int pressure(double dt) override { return pressure_impl((Real)(float)dt); }
-    int pressure_given_p(double dt) override { return grad_subtract((Real)(float)dt); }
+    int pressure(double dt) override {
+        if (int rc = pressure_impl((Real)(float)dt)) return rc;
+        return allgather_velocity();
+    }
+    int pressure_given_p(double dt) override {
+        if (int rc = grad_subtract((Real)(float)dt)) return rc;
+        return allgather_velocity();
+    }
 
     int poisson_solve(const void* b, void* p, int hd) override {
         if (int rc = check_hd(hd, err)) return rc;
@@ -737,27 +882,42 @@ struct Ctx final : CtxBase {
         Real* x = curl[0];   // scratch: curl is rewritten by the next vorticity phase before use
         CK(cudaMemsetAsync(x, 0, (size_t)g.n * sizeof(Real), stream));
         if (int rc = cg_solve(rhs, x)) return rc;
+        if (int rc = allgather_rows(x, sizeof(Real))) return rc;
         return grid_out_any(x, p, hd);
     }
 
     int vorticity_impl(Real dt) {
-        LAUNCH((k_curl<Real>), cell_blocks(), 256, g, U(0), U(1), U(2), curl[0], curl[1], curl[2]);
+        { const Grid q = slab(1); LAUNCH((k_curl<Real>), cell_blocks(q), 256, q, U(0), U(1), U(2), curl[0], curl[1], curl[2]); }
         CK(cudaMemsetAsync(d_scal, 0, sizeof(unsigned int), stream));
         LAUNCH((k_vorticity<Real>), cell_blocks(), 256, g, dt, C.kvort, curl[0], curl[1], curl[2], U(0), U(1), U(2), d_scal);
         CK(cudaGetLastError());
+        if (int rc = allreduce(d_scal, 1, ncclUint32, ncclMax)) return rc;
         maxv_valid = true;   // fused K0
         return 0;
     }
-    int vorticity(double dt) override { return vorticity_impl((Real)(float)dt); }
-
-    int velocity_field_update(double dt_) override {
-        const Real dt = (Real)(float)dt_;
-        if (int rc = advect_impl(dt, true)) return rc;
-        if (int rc = forces_impl(dt)) return rc;
-        if (int rc = viscosity_impl(dt)) return rc;
-        if (int rc = pressure_impl(dt)) return rc;
-        return vorticity_impl(dt);
+    // stand-alone hook: the velocity is valid on every row (previous all-gather), so curl's one-row redundancy is exact
+    int vorticity(double dt) override {
+        if (int rc = vorticity_impl((Real)(float)dt)) return rc;
+        return allgather_velocity();
     }
+
+    // System::updateVelocityField (src/waterSolver.cpp:41-96).  Multi-GPU: each phase runs on this rank's rows widened by the
+    // rows the LATER stencil phases will read (forces 3, viscosity 2, projection 2, curl 1, confinement 0), then the
+    // owners' rows are all-gathered once: every rank needs the whole field for its particle shard anyway.
+    int water_phases(Real dt, bool timed) {
+        if (int rc = advect_impl(dt, true, 3)) return rc;
+        if (timed) CK(cudaEventRecord(ev[2], stream));
+        if (int rc = forces_impl(dt, 3)) return rc;
+        if (timed) CK(cudaEventRecord(ev[3], stream));
+        if (int rc = viscosity_impl(dt, 2)) return rc;
+        if (timed) CK(cudaEventRecord(ev[4], stream));
+        if (int rc = pressure_impl(dt, 2)) return rc;
+        if (timed) CK(cudaEventRecord(ev[5], stream));
+        if (int rc = vorticity_impl(dt)) return rc;
+        return allgather_velocity();
+    }
+
+    int velocity_field_update(double dt_) override { return water_phases((Real)(float)dt_, false); }
 
     int particles_impl(Real dt) {
         if (np == 0) return 0;
@@ -771,6 +931,7 @@ struct Ctx final : CtxBase {
         // K8 seeded the mask from the new positions, and the wall clamp put every particle inside the grid; phantom
         // cells created earlier persist in the reference's map (their velocity keeps entering calcTimeStep)
         seed_valid = true;
+        seed_global = false;
         oob_now = false;
         ++since_sort;
         return 0;
@@ -788,15 +949,7 @@ struct Ctx final : CtxBase {
         if (int rc = calc_dt(ttnr, &dt_)) return rc;
         const Real dt = (Real)(float)dt_;   // `float timeStep` parameters narrow the double (Q15)
         CK(cudaEventRecord(ev[1], stream));
-        if (int rc = advect_impl(dt, true)) return rc;
-        CK(cudaEventRecord(ev[2], stream));
-        if (int rc = forces_impl(dt)) return rc;
-        CK(cudaEventRecord(ev[3], stream));
-        if (int rc = viscosity_impl(dt)) return rc;
-        CK(cudaEventRecord(ev[4], stream));
-        if (int rc = pressure_impl(dt)) return rc;
-        CK(cudaEventRecord(ev[5], stream));
-        if (int rc = vorticity_impl(dt)) return rc;
+        if (int rc = water_phases(dt, true)) return rc;
         CK(cudaEventRecord(ev[6], stream));
         if (int rc = particles_impl(dt)) return rc;
         CK(cudaEventRecord(ev[7], stream));
@@ -836,7 +989,15 @@ void ink_default_params(ink_params* p) {
     p->rank = 0; p->world_size = 1;
 }
 
-int ink_nccl_unique_id(uint8_t out[128]) { memset(out, 0, 128); return 0; }
+int ink_nccl_unique_id(uint8_t out[128]) {
+    memset(out, 0, 128);
+    const std::string e = nccl().load();
+    if (!e.empty()) { g_create_error = e; return 4; }
+    ncclUniqueId id;
+    if (nccl().GetUniqueId(&id) != ncclSuccess) { g_create_error = "ncclGetUniqueId failed"; return 4; }
+    memcpy(out, &id, sizeof id);
+    return 0;
+}
 
 int ink_create(const ink_params* p, ink_ctx** out) {
     if (!p || !out) return 2;

@@ -23,7 +23,8 @@ struct CgScal {
     double rz, rz_old;   // <r, z> for preconditioned CG (z = B r); plain CG keeps rz == rr
     int iters, done;
     unsigned int ticket;
-    int pad;
+    int dist;            // multi-GPU: kernels deposit THIS RANK's partial sums in loc[]; after the NCCL all-reduce k_cg_post applies them
+    double loc[4];       // [0] <d,w>  [1] <r,r>  [2] <r,z>  [3] <f,f>
     double partial[2][kCgMaxBlocks];
 };
 
@@ -134,10 +135,13 @@ __global__ void __launch_bounds__(256) k_cg_init(Grid g, CgScal* S, const Real* 
             for (int q = lane; q < (int)gridDim.x; q += 32) s += __ldcg(&S->partial[1][q]);
             tot_bb = warp_sum(s);
             if (lane == 0) {
-                S->rr = tot_rr; S->rr_old = tot_rr; S->bb = tot_bb; S->dw = 0;
-                S->rz = tot_rr; S->rz_old = tot_rr;
-                S->iters = 0;
-                S->done = (tot_rr <= S->tol2 * tot_bb) ? 1 : 0;
+                if (S->dist) { S->loc[1] = tot_rr; S->loc[3] = tot_bb; S->loc[0] = 0; S->loc[2] = 0; }
+                else {
+                    S->rr = tot_rr; S->rr_old = tot_rr; S->bb = tot_bb; S->dw = 0;
+                    S->rz = tot_rr; S->rz_old = tot_rr;
+                    S->iters = 0;
+                    S->done = (tot_rr <= S->tol2 * tot_bb) ? 1 : 0;
+                }
             }
         }
     }
@@ -145,7 +149,7 @@ __global__ void __launch_bounds__(256) k_cg_init(Grid g, CgScal* S, const Real* 
 
 template <class Real, int V>
 __global__ void __launch_bounds__(256) k_cg_dir_matvec(Grid g, CgScal* S, const Real* __restrict__ r, const Real* __restrict__ d,
-                                                       Real* __restrict__ dn, Real* __restrict__ w) {
+                                                       Real* __restrict__ dn, Real* __restrict__ w, int halo_lo, int halo_hi) {
     if (S->done) return;
     const Real beta = (S->iters == 0) ? Real(0) : (Real)(S->rz / S->rz_old);
     const int ZV = g.Z / V;
@@ -182,9 +186,26 @@ __global__ void __launch_bounds__(256) k_cg_dir_matvec(Grid g, CgScal* S, const 
         stp<Real, V>(dn + c, dnc);
         stp<Real, V>(w + c, wc);
     }
+    // multi-GPU: keep the direction current on the neighbour slabs' boundary rows too (d' = z + beta d is point-wise; z there
+    // arrived by halo exchange), so the next iteration can again recompute d' at the 6 neighbours without exchanging d
+    const int nh = halo_lo + halo_hi;
+    if (nh) {
+        const long long rowvec = (long long)g.X * ZV;
+        for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < nh * rowvec; t += (long long)gridDim.x * blockDim.x) {
+            const int h = (int)(t / rowvec);
+            const long long rem = t - h * rowvec;
+            const int j = (h == 0 && halo_lo) ? g.j0 - 1 : g.j1;
+            const long long c = (long long)j * g.sy + rem * V;
+            const Pack<Real, V> rc = ldp<Real, V>(r + c), dc = ldp<Real, V>(d + c);
+            Pack<Real, V> o;
+#pragma unroll
+            for (int a = 0; a < V; ++a) o.a[a] = rfma(beta, dc.a[a], rc.a[a]);
+            stp<Real, V>(dn + c, o);
+        }
+    }
     double tot;
     if (block_sum_last(acc, S, 0, tot)) {
-        if (threadIdx.x == 0) S->dw = tot;
+        if (threadIdx.x == 0) { if (S->dist) S->loc[0] = tot; else S->dw = tot; }
     }
 }
 
@@ -214,12 +235,39 @@ __global__ void __launch_bounds__(256) k_cg_update(Grid g, CgScal* S, Real* __re
     double tot;
     if (block_sum_last(acc, S, 1, tot)) {
         if (threadIdx.x == 0) {
-            S->rr_old = S->rr;
-            S->rr = tot;
-            if (!PRECOND) { S->rz_old = S->rz; S->rz = tot; }
-            S->iters += 1;
-            if (tot <= S->tol2 * S->bb) S->done = 1;
+            if (S->dist) S->loc[1] = tot;
+            else {
+                S->rr_old = S->rr;
+                S->rr = tot;
+                if (!PRECOND) { S->rz_old = S->rz; S->rz = tot; }
+                S->iters += 1;
+                if (tot <= S->tol2 * S->bb) S->done = 1;
+            }
         }
+    }
+}
+
+// Multi-GPU only: after ncclAllReduce(sum) of S->loc, one thread applies the global sums exactly like the fused single-GPU
+// epilogues do.  stage 0: after k_cg_init; 1: after k_cg_dir_matvec; 2: end of iteration (rr from k_cg_update, rz from the
+// V-cycle when preconditioned, else rz = rr); 3: <r,z> of the very first V-cycle.
+__global__ void k_cg_post(CgScal* S, int stage, int precond) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    if (stage == 0) {
+        S->rr = S->loc[1]; S->rr_old = S->loc[1]; S->bb = S->loc[3]; S->dw = 0;
+        S->rz = S->loc[1]; S->rz_old = S->loc[1];
+        S->iters = 0;
+        S->done = (S->loc[1] <= S->tol2 * S->loc[3]) ? 1 : 0;
+    } else if (S->done) {
+        return;
+    } else if (stage == 1) {
+        S->dw = S->loc[0];
+    } else if (stage == 2) {
+        S->rr_old = S->rr; S->rr = S->loc[1];
+        S->rz_old = S->rz; S->rz = precond ? S->loc[2] : S->loc[1];
+        S->iters += 1;
+        if (S->loc[1] <= S->tol2 * S->bb) S->done = 1;
+    } else {
+        S->rz_old = S->loc[2]; S->rz = S->loc[2];
     }
 }
 

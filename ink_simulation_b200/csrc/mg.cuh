@@ -196,7 +196,7 @@ __global__ void __launch_bounds__(256) k_mg_smooth(CgScal* S, MgDims d, Real s, 
     if (FINAL) {
         double tot;
         if (block_sum_last(acc, S, 0, tot)) {
-            if (threadIdx.x == 0) { S->rz_old = S->rz; S->rz = tot; }
+            if (threadIdx.x == 0) { if (S->dist) S->loc[2] = tot; else { S->rz_old = S->rz; S->rz = tot; } }
         }
     }
 }
@@ -275,7 +275,7 @@ __global__ void __launch_bounds__(kMgTailThreads) k_mg_tail(CgScal* S, MgTailArg
         if (threadIdx.x == 0) {
             double t = 0;
             for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += red[w];
-            S->rz_old = S->rz; S->rz = t;
+            if (S->dist) S->loc[2] = t; else { S->rz_old = S->rz; S->rz = t; }
         }
     }
 }

@@ -87,7 +87,7 @@ __global__ void __launch_bounds__(256) k_mg_smooth_v4(CgScal* S, MgDims d, Real 
     if (FINAL) {
         double tot;
         if (block_sum_last(acc, S, 0, tot)) {
-            if (threadIdx.x == 0) { S->rz_old = S->rz; S->rz = tot; }
+            if (threadIdx.x == 0) { if (S->dist) S->loc[2] = tot; else { S->rz_old = S->rz; S->rz = tot; } }
         }
     }
 }

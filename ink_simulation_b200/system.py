@@ -44,12 +44,45 @@ def _ptr(a):
     return C.c_void_p(int(a))
 
 
+def nccl_unique_id() -> bytes:
+    """ncclGetUniqueId on the calling rank (rank 0); broadcast the 128 bytes to the other ranks yourself."""
+    buf = (C.c_uint8 * 128)()
+    L = _capi.load()
+    if L.ink_nccl_unique_id(buf) != 0:
+        raise InkError(L.ink_last_error(None).decode())
+    return bytes(buf)
+
+
+def shard_range(n, rank, world_size):
+    """Index range [first, last) of an n-particle drop that `rank` keeps (same rule as ink_set_particles)."""
+    return n * rank // world_size, n * (rank + 1) // world_size
+
+
+def slab_range(Y, rank, world_size):
+    """Grid rows [j0, j1) that `rank` owns (same rule as ink_create)."""
+    return Y * rank // world_size, Y * (rank + 1) // world_size
+
+
+def create_distributed(X, Y, Z, **kw):
+    """One `System` per torch.distributed rank (launched by torchrun, backend nccl or gloo for the id exchange):
+    rank 0 creates the NCCL id, everyone receives it, every rank opens its own GPU (LOCAL_RANK)."""
+    import os
+
+    import torch.distributed as dist
+
+    rank, world = dist.get_rank(), dist.get_world_size()
+    box = [nccl_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0)
+    kw.setdefault("device", int(os.environ.get("LOCAL_RANK", rank)))
+    return System(X, Y, Z, rank=rank, world_size=world, nccl_id=box[0], **kw)
+
+
 class System:
     """Drop-in for the reference `System`: one MAC water grid + ink particle drops, stepped on one B200."""
 
     def __init__(self, X=20, Y=45, Z=20, dtype=np.float32, params: Params | None = None, arith="strict", device=0,
                  cg_rtol=None, cg_max_iters=None, cg_check_every=None, cg_warm_start=None, cg_precond=None,
-                 resort_interval=None):
+                 resort_interval=None, rank=0, world_size=1, nccl_id=None):
         self.L = _capi.load()
         self.dims = (int(X), int(Y), int(Z))
         self.dtype = np.dtype(dtype)
@@ -78,6 +111,14 @@ class System:
             p.cg_precond = {"none": _capi.PCG_NONE, "mg": _capi.PCG_MG}[cg_precond]
         if resort_interval is not None:
             p.resort_interval = resort_interval
+        # multi-GPU: one process per GPU; the grid is split in y-slabs, particles by index (include/ink_capi.h)
+        self.rank, self.world_size = int(rank), int(world_size)
+        p.rank, p.world_size = self.rank, self.world_size
+        if self.world_size > 1:
+            if nccl_id is None or len(nccl_id) != 128:
+                raise ValueError("world_size > 1 needs the 128-byte nccl_id from nccl_unique_id() of rank 0")
+            for i, b in enumerate(bytes(nccl_id)):
+                p.nccl_id[i] = b
         self._p = p
         h = C.c_void_p()
         rc = self.L.ink_create(C.byref(p), C.byref(h))
