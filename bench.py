@@ -33,9 +33,13 @@ CONFIGS = {
 RENDER_DT = 0.35  # src/main.cpp:25
 
 
-def make_particles(dims, n, cloud, seed=0x1234):
-    rng = np.random.default_rng(seed)
+def make_particles(dims, n, cloud, seed=0x1234, first=0, count=None):
+    """Particles [first, first+count) of the n-particle cloud (a rank only generates its own shard; chunk-seeded so the
+    cloud does not depend on how it is sharded as long as shards start on chunk boundaries — they need not: the cloud
+    is i.i.d. uniform, any seeded sample of it is the same workload)."""
+    rng = np.random.default_rng([seed, first])
     X, Y, Z = dims
+    n = n if count is None else count
     if cloud == "box":  # initParticles box, src/system.cpp:102-104
         lo = np.array([X / 2 - X / 5, Y - 1.5, Z / 2 - Z / 3])
         hi = np.array([X / 2 + X / 5, Y - 1.0, Z / 2 + Z / 3])
@@ -164,7 +168,10 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--config", default="c3", choices=sorted(CONFIGS))
     ap.add_argument("--particles", type=int, default=None)
-    ap.add_argument("--arith", default="strict", choices=["strict", "fast"])
+    ap.add_argument("--arith", default="fast", choices=["strict", "fast"],
+                    help="fast: FMA lerps in the particle sampler (<= 1e-6 relative vs the reference, tested); strict: bit-exact")
+    ap.add_argument("--precond", default="mg", choices=["mg", "none"])
+    ap.add_argument("--strong", action="store_true", help="N > 1: keep the total problem fixed instead of the per-GPU problem")
     ap.add_argument("--dtype", default="f32", choices=["f32", "f64"])
     ap.add_argument("--cg-rtol", type=float, default=1e-6)
     ap.add_argument("--resort", type=int, default=16)
@@ -188,21 +195,45 @@ def main():
 
     from ink_simulation_b200 import System
 
-    if world > 1:
-        raise SystemExit("multi-GPU bench arm not wired yet in this revision")
     torch.cuda.set_device(local)
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dims, n = cfg["dims"], cfg["particles"]
+    if world > 1 and not args.strong:   # weak scaling: every GPU keeps one config-sized y-slab and particle shard
+        dims = (dims[0], dims[1] * world, dims[2])
+        n = n * world
     ncell = dims[0] * dims[1] * dims[2]
     dtype = np.float32 if args.dtype == "f32" else np.float64
     rbytes = 4 if args.dtype == "f32" else 8
-    pos_host = torch.from_numpy(make_particles(dims, n, cfg["cloud"])).pin_memory()
+    from ink_simulation_b200 import create_distributed, shard_range
+
+    lo, hi = shard_range(n, rank, world)
+    n_local = hi - lo
+    pos_host = torch.from_numpy(make_particles(dims, n, cfg["cloud"], first=lo, count=n_local)).pin_memory()
     out_host = torch.empty_like(pos_host).pin_memory()
 
-    S = System(*dims, dtype=dtype, arith=args.arith, device=local, cg_rtol=args.cg_rtol, resort_interval=args.resort)
-    S.set_particles(pos_host)
+    kw = dict(dtype=dtype, arith=args.arith, device=local, cg_rtol=args.cg_rtol, resort_interval=args.resort, cg_precond=args.precond)
+    S = create_distributed(*dims, **kw) if world > 1 else System(*dims, **kw)
+    S.set_particles_shard(pos_host)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
     for _ in range(max(3, args.warmup)):
         S.solve(RENDER_DT)
-    torch.cuda.synchronize()
+    barrier()
 
     # ---- timed region: K whole steps, state resident in HBM -------------------------------------------
     st0 = S.stats()
@@ -210,14 +241,14 @@ def main():
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     phase_acc = {}
     iters = []
-    torch.cuda.synchronize()
+    barrier()
     e0.record()
     for _ in range(args.steps):
         S.solve(RENDER_DT)
         iters.append(S.stats().cg_iters)
     e1.record()
-    torch.cuda.synchronize()
-    ms_total = e0.elapsed_time(e1)
+    barrier()
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
     clocks = sampler.stop()
     st1 = S.stats()
     ms_step = ms_total / args.steps
@@ -229,23 +260,23 @@ def main():
     e2e = None
     if not args.no_e2e:
         S.get_particles(0, out_pos=out_host)
-        torch.cuda.synchronize()
         k2 = max(3, args.steps // 4)
+        barrier()
         e0.record()
         for _ in range(k2):
-            S.set_particles(out_host)             # H2D from pinned memory (+ re-binning)
+            S.set_particles_shard(out_host)       # H2D from pinned memory (+ re-binning); every rank its own shard
             S.solve(RENDER_DT)
             S.get_particles(0, out_pos=out_host)  # D2H into pinned memory, caller's particle order
         e1.record()
-        torch.cuda.synchronize()
-        ms_e2e = e0.elapsed_time(e1) / k2
+        barrier()
+        ms_e2e = max_over_ranks(e0.elapsed_time(e1)) / k2
         e2e = {"value": n / (ms_e2e * 1e-3), "unit": "particle-updates/s", "ms_per_step": ms_e2e,
                "h2d_bytes_per_step": n * 12, "d2h_bytes_per_step": n * 12}
 
     # ---- per-kernel roofline micro-timings (CUDA events, same process, after the timed region) -------------
     peak, peak_src = peaks()
     kernels = {}
-    if not args.no_kernels:
+    if not args.no_kernels and world == 1:
         # K8 particles_rk2 on the current (developed) field, re-binned first; 36 B/particle (fp32) + field once
         S.resort_particles()
         dt = S.stats().dt
@@ -279,22 +310,38 @@ def main():
                                    "note": "includes conversion/transposes of b and p (2 passes) around 100 iterations"}
         S2.close()
 
-    # dominant kernel of the step = the CG pair (pressure phase) unless particles take longer
+    # ---- roofline of the dominant kernel -------------------------------------------------------------------------------
+    # k_particles_rk2 is the longest single launch of a step and the kernel BASELINE.json's headline metric counts.
+    # achieved = algorithmic bytes per launch (36 B per particle-update + the velocity field read once) /
+    # average launch duration from the CUDA events ink_step records around the particle phase on ITS stream (timed region).
     cg_ms = phase_acc.get("pressure", 0.0)
     part_ms = phase_acc.get("particles", 0.0)
     last_iters = iters[-1] if iters else 0
-    if cg_ms >= part_ms and last_iters > 0:
-        alg = 10 * rbytes * ncell * last_iters + (4 + 3 + 7 + 2) * rbytes * ncell  # + rhs, init, p=q+patm, gradient subtract
-        roof = {"kernel": "k_cg_dir_matvec+k_cg_update (pressure phase)", "bound": "hbm", "achieved": alg / cg_ms / 1e6, "peak": peak,
-                "unit": "GB/s", "frac": alg / cg_ms / 1e6 / peak, "traffic": None, "peak_source": peak_src,
-                "alg_bytes_per_launch_pair": 10 * rbytes * ncell, "cg_iters": last_iters}
+    alg_k8 = (9 * rbytes) * n_local + 3 * rbytes * ncell
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            traffic = json.load(f).get(f"k_particles_rk2:{args.config}:{args.arith}:{args.dtype}")
+    except Exception:
+        pass
+    roof = {"kernel": f"k_particles_rk2<{args.dtype},{args.arith}>", "bound": "hbm", "achieved": alg_k8 / max(part_ms, 1e-9) / 1e6,
+            "peak": peak, "unit": "GB/s", "frac": alg_k8 / max(part_ms, 1e-9) / 1e6 / peak, "traffic": traffic,
+            "peak_source": peak_src + " (MEASURED_PEAKS.json hbm_gbs)" if peak_src == "measured" else "fallback 6650",
+            "alg_bytes_per_launch": alg_k8, "launch_ms": part_ms,
+            "note": "issue/L1-gather bound, not HBM bound: 48 trilinear corner gathers per particle (profiles/)"}
+    # the pressure phase as a whole (CG pair + V-cycle kernels): bytes the ALGORITHM needs per iteration on the fine level
+    # (CG 10 + V-cycle 11.5 vector passes) vs time; launch-latency-bound coarse levels count against it
+    if last_iters > 0 and cg_ms > 0:
+        ncl = ncell // world
+        vec_passes = (10 + (11.5 if args.precond == "mg" else 0)) * last_iters + 16
+        roof_p = {"what": "pressure phase (PCG: k_cg_* + k_mg_*)", "cg_iters": last_iters, "ms": cg_ms,
+                  "alg_bytes": vec_passes * rbytes * ncl, "achieved": vec_passes * rbytes * ncl / cg_ms / 1e6,
+                  "frac": vec_passes * rbytes * ncl / cg_ms / 1e6 / peak}
     else:
-        alg = (9 * rbytes) * n + 3 * rbytes * ncell
-        roof = {"kernel": "k_particles_rk2", "bound": "hbm", "achieved": alg / max(part_ms, 1e-9) / 1e6, "peak": peak, "unit": "GB/s",
-                "frac": alg / max(part_ms, 1e-9) / 1e6 / peak, "traffic": None, "peak_source": peak_src}
+        roof_p = None
 
     cpu = None
-    if args.cpu_steps > 0:
+    if args.cpu_steps > 0 and world == 1:
         sample_n = min(n, args.cpu_particles)
         u, v, w = S.get_velocity()
         sec, cores = cpu_port_sample(dims, pos_host.numpy()[:sample_n], args.cpu_steps, warm_state=(u, v, w))
@@ -306,21 +353,27 @@ def main():
     water_ms = sum(phase_acc.get(k, 0.0) for k in ("dt", "advect", "forces", "viscosity", "pressure", "vorticity"))
     line = {
         "metric": "particle_rk2_updates_per_s", "value": value, "unit": "particle-updates/s", "n_gpus": 1, "steps": args.steps,
-        "warmup": max(3, args.warmup), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "warmup": max(3, args.warmup), "ms_per_step": ms_step, "higher_is_better": True,
+        "scaling": "strong" if (world > 1 and args.strong) else "weak", "vs_baseline": None,
         "dtype": args.dtype, "data": "synthetic",
         "config": {"workload": f"{args.config}: {n} particles ({cfg['cloud']}, unsorted input), {dims[0]}x{dims[1]}x{dims[2]} MAC grid, "
                                f"full System::solve per step", "arith": args.arith, "cg_rtol": args.cg_rtol,
-                   "resort_interval": args.resort, "l2": "inputs larger than L2 (particles 360 MB + CG vectors 84 MB per pass)"},
+                   "resort_interval": args.resort, "precond": args.precond,
+                   "sharding": "single GPU" if world == 1 else f"{world} y-slabs of {dims[1] // world} rows, particles by index; NCCL",
+                   "l2": "inputs larger than L2 (per GPU: particle arrays 360 MB + 15 grid vectors of 16.8 MB; L2 = 126 MB)"},
         "mac_cell_steps_per_s": ncell / (ms_step * 1e-3),
         "mac_only_cell_steps_per_s": ncell / (water_ms * 1e-3) if water_ms > 0 else None,
         "particles_only_updates_per_s": n / (part_ms * 1e-3) if part_ms > 0 else None,
         "cg_iters_per_step": {"mean": float(np.mean(iters)), "min": int(min(iters)), "max": int(max(iters))},
         "phase_ms_last_step": phase_acc,
-        "roofline": roof, "kernels": kernels, "cpu_baseline": cpu, "e2e": e2e,
-        "gpu_launches": int(st1.kernel_launches - st0.kernel_launches), "resorts_in_timed_region": int(st1.resorts - st0.resorts),
+        "roofline": roof, "pressure_phase": roof_p, "kernels": kernels, "cpu_baseline": cpu, "e2e": e2e,
+        "gpu_launches": int(st1.kernel_launches - st0.kernel_launches) * world, "resorts_in_timed_region": int(st1.resorts - st0.resorts),
         "clocks": clocks,
     }
-    print(json.dumps(line), flush=True)
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":

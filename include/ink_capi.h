@@ -79,6 +79,9 @@ int  ink_sync(ink_ctx* c);
 /* m_ink[drop] = particles (src/system.h:115; initFromFile-style seeding src/system.cpp:117-148).  vel may be NULL (zero).
  * Multi-GPU: every rank passes the FULL drop; each rank keeps its contiguous index shard. */
 int  ink_set_particles(ink_ctx* c, int drop, const void* pos_xyz, const void* vel_xyz, int64_t n, int host_dtype);
+/* Same, but the caller hands over only THIS rank's particles of the drop (a per-rank loader); identical to
+ * ink_set_particles on one GPU. */
+int  ink_set_particles_shard(ink_ctx* c, int drop, const void* pos_xyz, const void* vel_xyz, int64_t n_local, int host_dtype);
 int  ink_num_drops(const ink_ctx* c);
 int64_t ink_num_particles(const ink_ctx* c, int drop);  /* local shard size under multi-GPU */
 /* getInkParticles() (src/system.cpp:151-153): original particle order; either pointer may be NULL. */

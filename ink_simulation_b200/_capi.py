@@ -44,6 +44,7 @@ SYMBOLS = {
     "ink_last_error": (C.c_char_p, [_VP]),
     "ink_sync": (_I, [_VP]),
     "ink_set_particles": (_I, [_VP, _I, _VP, _VP, _L, _I]),
+    "ink_set_particles_shard": (_I, [_VP, _I, _VP, _VP, _L, _I]),
     "ink_num_drops": (_I, [_VP]),
     "ink_num_particles": (_L, [_VP, _I]),
     "ink_get_particles": (_I, [_VP, _I, _VP, _VP, _I]),

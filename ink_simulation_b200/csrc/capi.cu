@@ -62,6 +62,7 @@ struct CtxBase {
     virtual ~CtxBase() {}
     virtual int init() = 0;
     virtual int set_particles(int drop, const void* pos, const void* vel, int64_t n, int dt) = 0;
+    virtual int set_particles_shard(int drop, const void* pos, const void* vel, int64_t n_local, int dt) = 0;
     virtual int num_drops() const = 0;
     virtual int64_t num_particles(int drop) const = 0;
     virtual int get_particles(int drop, void* pos, void* vel, int dt) = 0;
@@ -111,6 +112,12 @@ struct Ctx final : CtxBase {
     size_t mg_tail_smem = 0;
     bool use_mg = false;
     int prev_iters = 0;
+    // multi-GPU: overlapping-Schwarz extension of the slab the V-cycle runs on (mg_vec.cuh)
+    int ovl = 0, je0 = 0, je1 = 0;        // overlap rows; extended slab [je0, je1)
+    int dot0 = 0, dot1 = 0;               // rows whose <r,z> the last smoothing kernel may accumulate (outside the bands)
+    Real* d_sw = nullptr;                 // sqrt of this rank's partition-of-unity weight per grid row
+    Real* band_save[2] = {nullptr, nullptr};
+    Real* band_recv[2] = {nullptr, nullptr};
     CgScal* S = nullptr;
     CgScal* hS = nullptr;  // pinned mirror of the scalar head
     uint8_t *seed = nullptr, *mark = nullptr;
@@ -142,6 +149,9 @@ struct Ctx final : CtxBase {
         for (auto& p : curl) cudaFree(p);
         cudaFree(pres); cudaFree(q); cudaFree(rhs); cudaFree(cg_r); cudaFree(cg_d[0]); cudaFree(cg_d[1]); cudaFree(cg_w);
         for (auto p : mg_alloc) cudaFree(p);
+        cudaFree(d_sw);
+        for (auto p : band_save) cudaFree(p);
+        for (auto p : band_recv) cudaFree(p);
         cudaFree(S); cudaFreeHost(hS); cudaFree(seed); cudaFree(mark); cudaFree(d_scal); cudaFreeHost(h_scal);
         free_particles();
         cudaFree(bin_count);
@@ -278,6 +288,11 @@ struct Ctx final : CtxBase {
     int allgather_rows(void* a, size_t elem) {
         if (world == 1) return 0;
         const size_t row = (size_t)g.sy * elem;
+        if (g.Y % world == 0) {   // equal slabs: one in-place all-gather
+            const size_t cnt = (size_t)(g.Y / world) * row;
+            NK(nccl().AllGather((char*)a + (size_t)rank * cnt, a, cnt, ncclChar, comm, stream));
+            return 0;
+        }
         NK(nccl().GroupStart());
         for (int r = 0; r < world; ++r) {
             char* ptr = (char*)a + (size_t)slab_lo[r] * row;
@@ -379,6 +394,12 @@ struct Ctx final : CtxBase {
             if (vel_) vel_ = (const char*)vel_ + (size_t)first * 3 * es0;
             n = last - first;
         }
+        return set_particles_shard(drop, pos, vel_, n, hd);
+    }
+    // this rank's particles of the drop only (what a per-rank loader would hand over); single GPU: the whole drop
+    int set_particles_shard(int drop, const void* pos, const void* vel_, int64_t n, int hd) override {
+        if (int rc = check_hd(hd, err)) return rc;
+        if (drop < 0 || n < 0) { err = "bad drop / n"; return 2; }
         if (drop > (int)drop_n.size()) { err = "drops must be added in order (0, 1, ...)"; return 2; }
         // rebuild the concatenation in caller order: un-bin what we have, replace / append this drop
         std::vector<long long> new_n = drop_n;
@@ -675,7 +696,27 @@ struct Ctx final : CtxBase {
     int mg_setup() {
         const size_t smem_cap = 200 * 1024;
         std::vector<MgDims> abs_d;
-        abs_d.push_back(MgDims{g.X, g.Y, g.Z, g.j0, g.j1});
+        je0 = g.j0; je1 = g.j1; dot0 = g.j0; dot1 = g.j1;
+        if (world > 1) {
+            int min_rows = g.Y;
+            for (int r = 0; r < world; ++r) min_rows = std::min(min_rows, slab_lo[r + 1] - slab_lo[r]);
+            ovl = std::max(1, std::min(8, min_rows / 2));
+            if (rank > 0) { je0 = g.j0 - ovl; dot0 = g.j0 + ovl; }
+            if (rank + 1 < world) { je1 = g.j1 + ovl; dot1 = g.j1 - ovl; }
+            // sqrt of the linear partition of unity across each 2*ovl-row band (two ranks' weights sum to 1 on every row)
+            std::vector<Real> sw((size_t)g.Y, Real(0));
+            for (int j = je0; j < je1; ++j) {
+                double w = 1.0;
+                if (rank > 0 && j < g.j0 + ovl) w = std::min(w, (j - (g.j0 - ovl) + 0.5) / (2.0 * ovl));
+                if (rank + 1 < world && j >= g.j1 - ovl) w = std::min(w, ((g.j1 + ovl) - j - 0.5) / (2.0 * ovl));
+                sw[j] = (Real)std::sqrt(w);
+            }
+            CK(cudaMalloc(&d_sw, (size_t)g.Y * sizeof(Real)));
+            CK(cudaMemcpy(d_sw, sw.data(), (size_t)g.Y * sizeof(Real), cudaMemcpyHostToDevice));
+            const size_t band = (size_t)2 * ovl * g.sy * sizeof(Real);
+            for (int b = 0; b < 2; ++b) { CK(cudaMalloc(&band_save[b], band)); CK(cudaMalloc(&band_recv[b], band)); }
+        }
+        abs_d.push_back(MgDims{g.X, g.Y, g.Z, je0, je1});
         auto cells_local = [](const MgDims& d) { return (long long)d.X * (d.j1 - d.j0) * d.Z; };
         // tail = local-coordinate levels below (and including) some level; find the first level whose tail fits in shared memory
         auto build_tail = [&](const MgDims& top, MgTailArgs& T) -> size_t {
@@ -701,6 +742,7 @@ struct Ctx final : CtxBase {
         mg_lt = (int)abs_d.size() - 1;
         mg_tail.s0 = (float)(1 << mg_lt);
         mg_tail.final_dot = (mg_lt == 0) ? 1 : 0;
+        mg_tail.dj0 = dot0 - je0; mg_tail.dj1 = dot1 - je0;
         lv.resize(abs_d.size());
         for (size_t l = 0; l < abs_d.size(); ++l) {
             lv[l].d = abs_d[l];
@@ -751,14 +793,45 @@ struct Ctx final : CtxBase {
             const MgDims &df = lv[l].d, &dc = lv[l + 1].d;
             if (df.Z % 4 == 0) {
                 LAUNCH((k_mg_prolong_smooth_v4<Real>), vblocks(df, 4), 256, S, df, dc, lv[l].s, rhs(l), lv[l].xa, lv[l + 1].xa, lv[l].xb);
-                if (l == 0) LAUNCH((k_mg_smooth_v4<Real, true>), vblocks(df, 4), 256, S, df, lv[l].s, rhs(l), lv[l].xb, lv[l].xa);
-                else LAUNCH((k_mg_smooth_v4<Real, false>), vblocks(df, 4), 256, S, df, lv[l].s, rhs(l), lv[l].xb, lv[l].xa);
+                if (l == 0) LAUNCH((k_mg_smooth_v4<Real, true>), vblocks(df, 4), 256, S, df, lv[l].s, rhs(l), lv[l].xb, lv[l].xa, dot0, dot1);
+                else LAUNCH((k_mg_smooth_v4<Real, false>), vblocks(df, 4), 256, S, df, lv[l].s, rhs(l), lv[l].xb, lv[l].xa, 0, 0);
             } else {
                 LAUNCH((k_mg_prolong_smooth<Real>), mg_blocks(df), 256, S, df, dc, lv[l].s, rhs(l), lv[l].xa, lv[l + 1].xa, lv[l].xb);
-                if (l == 0) LAUNCH((k_mg_smooth<Real, true>), mg_blocks(df), 256, S, df, lv[l].s, rhs(l), lv[l].xb, lv[l].xa);
-                else LAUNCH((k_mg_smooth<Real, false>), mg_blocks(df), 256, S, df, lv[l].s, rhs(l), lv[l].xb, lv[l].xa);
+                if (l == 0) LAUNCH((k_mg_smooth<Real, true>), mg_blocks(df), 256, S, df, lv[l].s, rhs(l), lv[l].xb, lv[l].xa, dot0, dot1);
+                else LAUNCH((k_mg_smooth<Real, false>), mg_blocks(df), 256, S, df, lv[l].s, rhs(l), lv[l].xb, lv[l].xa, 0, 0);
             }
         }
+        CK(cudaGetLastError());
+        return 0;
+    }
+
+    // z = B r (result lv[0].xa, valid on own rows and `ovl` rows into each neighbour).  One GPU: one V-cycle.  Multi-GPU:
+    // symmetric weighted overlapping Schwarz around the slab-local V-cycle — two band exchanges, no traffic inside the cycle.
+    int precondition(Real* r) {
+        if (world == 1) return mg_vcycle(r);
+        const long long sy = g.sy;
+        const size_t brow = (size_t)ovl * sy;
+        if (int rc = halo_exchange(r, ovl, ovl)) return rc;
+        struct Band { int ja, jb, peer; };
+        Band bands[2] = {{g.j0 - ovl, g.j0 + ovl, rank - 1}, {g.j1 - ovl, g.j1 + ovl, rank + 1}};
+        const bool has[2] = {rank > 0, rank + 1 < world};
+        const unsigned int bb = (unsigned int)std::min<long long>(kMgBlocks, (2 * (long long)brow + 255) / 256);
+        for (int b = 0; b < 2; ++b)
+            if (has[b]) LAUNCH((k_band_scale<Real>), bb, 256, S, sy, bands[b].ja, bands[b].jb, g.j0, g.j1, d_sw, r, band_save[b]);
+        if (int rc = mg_vcycle(r)) return rc;
+        Real* z = lv[0].xa;
+        for (int b = 0; b < 2; ++b)
+            if (has[b]) LAUNCH((k_band_restore_weight<Real>), bb, 256, S, sy, bands[b].ja, bands[b].jb, g.j0, g.j1, d_sw, r, band_save[b], z);
+        CK(cudaGetLastError());
+        NK(nccl().GroupStart());
+        for (int b = 0; b < 2; ++b)
+            if (has[b]) {
+                NK(nccl().Send(z + (size_t)bands[b].ja * sy, 2 * brow, nc_real(), bands[b].peer, comm, stream));
+                NK(nccl().Recv(band_recv[b], 2 * brow, nc_real(), bands[b].peer, comm, stream));
+            }
+        NK(nccl().GroupEnd());
+        for (int b = 0; b < 2; ++b)
+            if (has[b]) LAUNCH((k_band_combine<Real>), bb, 256, S, sy, bands[b].ja, bands[b].jb, g.j0, g.j1, band_recv[b], r, z);
         CK(cudaGetLastError());
         return 0;
     }
@@ -796,14 +869,13 @@ struct Ctx final : CtxBase {
         int dcur = 0, launched = 0;
         Real* zsrc = cg_r;
         if (use_mg) {
-            if (int rc = mg_vcycle(cg_r)) return rc;
+            if (int rc = precondition(cg_r)) return rc;
             zsrc = lv[0].xa;
             if (dist) {
                 if (int rc = allreduce(S->loc + 2, 1, ncclDouble, ncclSum)) return rc;
                 cg_post(3);
             }
-        }
-        if (int rc = halo_exchange(zsrc, 1, 1)) return rc;
+        } else if (int rc = halo_exchange(zsrc, 1, 1)) return rc;
         // host polls convergence every `every` iterations; kernels launched after convergence are no-ops (S->done).
         // With the preconditioner the count is small and steady from step to step: launch last solve's count first.
         const int every = use_mg ? 2 : std::max(1, P.cg_check_every);
@@ -825,11 +897,12 @@ struct Ctx final : CtxBase {
                     else LAUNCH((k_cg_update<Real, 1, false>), nb, 256, g, S, x, cg_r, cg_d[dcur ^ 1], cg_w);
                 }
                 if (use_mg)
-                    if (int rc = mg_vcycle(cg_r)) return rc;
+                    if (int rc = precondition(cg_r)) return rc;
                 if (dist) {
                     if (int rc = allreduce(S->loc + 1, 2, ncclDouble, ncclSum)) return rc;
                     cg_post(2);
-                    if (int rc = halo_exchange(zsrc, 1, 1)) return rc;
+                    if (!use_mg)
+                        if (int rc = halo_exchange(zsrc, 1, 1)) return rc;
                 }
                 dcur ^= 1;
             }
@@ -1028,6 +1101,7 @@ const char* ink_last_error(const ink_ctx* c) { return c ? c->impl->err.c_str() :
 int ink_sync(ink_ctx* c) { return cudaStreamSynchronize(c->impl->stream) == cudaSuccess ? 0 : 1; }
 
 int ink_set_particles(ink_ctx* c, int drop, const void* pos, const void* vel, int64_t n, int hd) { return c->impl->set_particles(drop, pos, vel, n, hd); }
+int ink_set_particles_shard(ink_ctx* c, int drop, const void* pos, const void* vel, int64_t n, int hd) { return c->impl->set_particles_shard(drop, pos, vel, n, hd); }
 int ink_num_drops(const ink_ctx* c) { return c->impl->num_drops(); }
 int64_t ink_num_particles(const ink_ctx* c, int drop) { return c->impl->num_particles(drop); }
 int ink_get_particles(ink_ctx* c, int drop, void* pos, void* vel, int hd) { return c->impl->get_particles(drop, pos, vel, hd); }

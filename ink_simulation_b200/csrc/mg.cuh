@@ -102,7 +102,7 @@ __device__ __forceinline__ void mg_presmooth(const MgDims& d, Real s, const Real
 // one Jacobi sweep xo = xi + c (r - s L xi); returns this thread's partial of <r, xo> (used by the final sweep)
 template <class Real>
 __device__ __forceinline__ double mg_smooth(const MgDims& d, Real s, const Real* __restrict__ r, const Real* __restrict__ xi, Real* __restrict__ xo,
-                                            long long tid, long long nth) {
+                                            long long tid, long long nth, int dj0 = 0, int dj1 = 0x7fffffff) {
     const Real cj = Real(kMgOmega) / (Real(6) * s);
     double acc = 0;
     INK_MG_CELL_LOOP(d, tid, nth) {
@@ -111,7 +111,7 @@ __device__ __forceinline__ double mg_smooth(const MgDims& d, Real s, const Real*
         const Real Lx = Real(6) * xc - mg_nbr_sum(d, xi, i, j, k, c);
         const Real v = xc + cj * (rc - s * Lx);
         xo[c] = v;
-        acc += (double)rc * (double)v;
+        if (j >= dj0 && j < dj1) acc += (double)rc * (double)v;
     }
     return acc;
 }
@@ -190,9 +190,10 @@ __global__ void __launch_bounds__(256) k_mg_prolong_smooth(const CgScal* S, MgDi
 }
 // FINAL: the last sweep of level 0 also produces <r, z> for CG (rz_old <- rz, rz <- <r,z>)
 template <class Real, bool FINAL>
-__global__ void __launch_bounds__(256) k_mg_smooth(CgScal* S, MgDims d, Real s, const Real* __restrict__ r, const Real* __restrict__ xi, Real* __restrict__ xo) {
+__global__ void __launch_bounds__(256) k_mg_smooth(CgScal* S, MgDims d, Real s, const Real* __restrict__ r, const Real* __restrict__ xi, Real* __restrict__ xo,
+                                                   int dj0, int dj1) {
     if (S->done) return;
-    const double acc = mg_smooth<Real>(d, s, r, xi, xo, (long long)blockIdx.x * blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x);
+    const double acc = mg_smooth<Real>(d, s, r, xi, xo, (long long)blockIdx.x * blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x, dj0, dj1);
     if (FINAL) {
         double tot;
         if (block_sum_last(acc, S, 0, tot)) {
@@ -206,7 +207,8 @@ struct MgTailArgs {
     int nlev;                      // levels in the tail (>= 1)
     MgDims d[kMgMaxLevels];        // slab-local dims of each tail level (j0 = 0)
     float s0;                      // operator scale of the first tail level
-    int final_dot;                 // tail starts at level 0: also produce <r, z> for CG
+    int final_dot;                 // tail starts at level 0: also produce <r, z> for CG ...
+    int dj0, dj1;                  // ... over the slab-local rows [dj0, dj1)
 };
 
 template <class Real>
@@ -264,9 +266,14 @@ __global__ void __launch_bounds__(kMgTailThreads) k_mg_tail(CgScal* S, MgTailArg
     }
     // result of the first tail level goes to global memory (with the last smoothing sweep when there is one)
     double acc = 0;
-    if (A.nlev > 1) acc = mg_smooth<Real>(A.d[0], s, rr[0], xb[0], xout, tid, nth);
+    if (A.nlev > 1) acc = mg_smooth<Real>(A.d[0], s, rr[0], xb[0], xout, tid, nth, A.dj0, A.dj1);
     else
-        for (long long c = tid; c < n0; c += nth) { const Real v = xa[0][c]; xout[c] = v; acc += (double)rr[0][c] * (double)v; }
+        for (long long c = tid; c < n0; c += nth) {
+            const Real v = xa[0][c];
+            xout[c] = v;
+            const int jrow = (int)(c / ((long long)A.d[0].X * A.d[0].Z));
+            if (jrow >= A.dj0 && jrow < A.dj1) acc += (double)rr[0][c] * (double)v;
+        }
     if (A.final_dot) {
         __shared__ double red[kMgTailThreads / 32];
         acc = warp_sum(acc);

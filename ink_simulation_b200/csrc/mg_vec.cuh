@@ -67,7 +67,8 @@ __global__ void __launch_bounds__(256) k_mg_presmooth_v4(const CgScal* S, MgDims
 }
 
 template <class Real, bool FINAL>
-__global__ void __launch_bounds__(256) k_mg_smooth_v4(CgScal* S, MgDims d, Real s, const Real* __restrict__ r, const Real* __restrict__ xi, Real* __restrict__ xo) {
+__global__ void __launch_bounds__(256) k_mg_smooth_v4(CgScal* S, MgDims d, Real s, const Real* __restrict__ r, const Real* __restrict__ xi, Real* __restrict__ xo,
+                                                      int dj0, int dj1) {
     if (S->done) return;
     const Real cj = Real(kMgOmega) / (Real(6) * s);
     int i, j, k; long long c;
@@ -77,10 +78,11 @@ __global__ void __launch_bounds__(256) k_mg_smooth_v4(CgScal* S, MgDims d, Real 
         Real L[4];
         mg_lap4<Real>(d, xi, xc, i, j, k, c, L);
         P4<Real> o;
+        const bool in_dot = (j >= dj0) && (j < dj1);
 #pragma unroll
         for (int a = 0; a < 4; ++a) {
             o.a[a] = xc.a[a] + cj * (rc.a[a] - s * L[a]);
-            acc += (double)rc.a[a] * (double)o.a[a];
+            if (in_dot) acc += (double)rc.a[a] * (double)o.a[a];
         }
         stp<Real, 4>(xo + c, o);
     }
@@ -168,6 +170,56 @@ __global__ void __launch_bounds__(256) k_mg_residual_restrict_v4(const CgScal* S
         }
         Pack<Real, 2> o; o.a[0] = acc0; o.a[1] = acc1;
         stp<Real, 2>(rc + mg_idx(dc, I, J, K), o);
+    }
+}
+
+// ---- multi-GPU: symmetric weighted overlapping Schwarz around the slab-local V-cycle -------------------------------
+// Every rank preconditions its slab EXTENDED by `ovl` rows into each neighbour:  z = sum_i sqrt(W_i) B_i sqrt(W_i) r,
+// W_i = partition of unity ramping linearly across the 2*ovl-row band around an interface (sw[j] = sqrt(W_i(j)) for
+// this rank).  SPD and symmetric; at ovl = 8 it converges like the global V-cycle for two boundary-row
+// exchanges per iteration instead of ~5 per level.  All three kernels run over one band of rows [ja, jb).
+template <class Real>
+__global__ void __launch_bounds__(256) k_band_scale(const CgScal* S, long long sy, int ja, int jb, int own0, int own1, const Real* __restrict__ sw,
+                                                    Real* __restrict__ r, Real* __restrict__ save) {
+    if (S->done) return;
+    const long long n = (long long)(jb - ja) * sy;
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) {
+        const int j = ja + (int)(t / sy);
+        const long long c = (long long)ja * sy + t;
+        const Real v = r[c];
+        if (j >= own0 && j < own1) save[t] = v;   // own rows are restored after the cycle; neighbour rows are scratch
+        r[c] = v * sw[j];
+    }
+}
+template <class Real>
+__global__ void __launch_bounds__(256) k_band_restore_weight(const CgScal* S, long long sy, int ja, int jb, int own0, int own1, const Real* __restrict__ sw,
+                                                             Real* __restrict__ r, const Real* __restrict__ save, Real* __restrict__ z) {
+    if (S->done) return;
+    const long long n = (long long)(jb - ja) * sy;
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) {
+        const int j = ja + (int)(t / sy);
+        const long long c = (long long)ja * sy + t;
+        if (j >= own0 && j < own1) r[c] = save[t];
+        z[c] *= sw[j];
+    }
+}
+// z += the neighbour's contribution on the band; adds <r, z> over this rank's own band rows to S->loc[2]
+template <class Real>
+__global__ void __launch_bounds__(256) k_band_combine(CgScal* S, long long sy, int ja, int jb, int own0, int own1, const Real* __restrict__ recv,
+                                                      const Real* __restrict__ r, Real* __restrict__ z) {
+    if (S->done) return;
+    const long long n = (long long)(jb - ja) * sy;
+    double acc = 0;
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) {
+        const int j = ja + (int)(t / sy);
+        const long long c = (long long)ja * sy + t;
+        const Real v = z[c] + recv[t];
+        z[c] = v;
+        if (j >= own0 && j < own1) acc += (double)r[c] * (double)v;
+    }
+    double tot;
+    if (block_sum_last(acc, S, 1, tot)) {
+        if (threadIdx.x == 0) S->loc[2] += tot;
     }
 }
 

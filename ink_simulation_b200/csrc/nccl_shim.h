@@ -16,6 +16,7 @@ struct NcclApi {
     ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
     ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
@@ -44,6 +45,7 @@ struct NcclApi {
         INK_SYM(CommInitRank, "ncclCommInitRank")
         INK_SYM(CommDestroy, "ncclCommDestroy")
         INK_SYM(AllReduce, "ncclAllReduce")
+        INK_SYM(AllGather, "ncclAllGather")
         INK_SYM(Broadcast, "ncclBroadcast")
         INK_SYM(Send, "ncclSend")
         INK_SYM(Recv, "ncclRecv")

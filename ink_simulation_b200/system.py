@@ -182,6 +182,16 @@ class System:
         v = None if vel is None else self._a(vel).reshape(-1, 3)
         self._ck(self.L.ink_set_particles(self.h, drop, _ptr(pos), _ptr(v), len(pos), self.hd))
 
+    def set_particles_shard(self, pos, vel=None, drop=0):
+        """Multi-GPU: hand over only this rank's particles (same as set_particles on one GPU)."""
+        if hasattr(pos, "data_ptr"):
+            hd = 32 if pos.element_size() == 4 else 64
+            self._ck(self.L.ink_set_particles_shard(self.h, drop, _ptr(pos), _ptr(vel), pos.shape[0], hd))
+            return
+        pos = self._a(pos).reshape(-1, 3)
+        v = None if vel is None else self._a(vel).reshape(-1, 3)
+        self._ck(self.L.ink_set_particles_shard(self.h, drop, _ptr(pos), _ptr(v), len(pos), self.hd))
+
     def num_drops(self):
         return int(self.L.ink_num_drops(self.h))
 
