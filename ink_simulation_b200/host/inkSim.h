@@ -1,0 +1,35 @@
+// inkSim.h — drop-in for the reference's src/inkSim.h: same class, same constructor, same simulate() signature.
+#ifndef INK_SIM_H
+#define INK_SIM_H
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "system.h"
+
+class InkSim {
+public:
+    /// @param writeDirectory the path to the *directory* to save ply files to
+    InkSim(std::string writeDirectory);
+    ~InkSim();
+
+    /// run the ink simulation: a frame is written every `renderTimestep` of simulated time, `totalTimesteps` solver steps
+    void simulate(const float renderTimestep, int totalTimesteps);
+
+private:
+    System ink_system;
+    std::string writeDirectory;
+
+    void writeToFile(int frameNum);
+    void writeWaterGridVelocities();
+
+    // asynchronous frame output: positions land in one of two pinned host buffers, a writer thread streams the
+    // previous frame to disk while the GPU already computes the next steps
+    struct FrameBuf { float* host = nullptr; size_t cap = 0; std::thread writer; };
+    FrameBuf m_buf[2];
+    int m_cur = 0;
+    float* stage(FrameBuf& b, size_t floats);
+    void drain();
+};
+
+#endif  // INK_SIM_H

@@ -1,0 +1,100 @@
+// seeding.cpp — see seeding.h.
+#include "seeding.h"
+
+#include <cmath>
+#include <cstdlib>
+#include <fstream>
+#include <sstream>
+#include <stdexcept>
+
+using Eigen::Vector3f;
+
+namespace inkseed {
+
+static double randBetween(double lo, double hi) { return lo + ((double)rand() / RAND_MAX) * (hi - lo); }
+
+// initParticles (src/system.cpp:93-115): per_drop[i] particles per drop, uniform (glibc rand(), never seeded) in the
+// box x in X/2 -+ X/5, y in [Y-1.5, Y-1], z in Z/2 -+ Z/3; draw order x, y, z.
+void box(int X, int Y, int Z, const std::vector<int>& per_drop, std::vector<std::vector<Particle>>& drops) {
+    for (size_t d = 0; d < per_drop.size(); ++d) {
+        std::vector<Particle> ink;
+        ink.reserve(per_drop[d]);
+        for (int n = 0; n < per_drop[d]; ++n) {
+            Particle p;
+            const float x = randBetween(X / 2.f - X / 5.f, X / 2.f + X / 5.f);
+            const float y = randBetween(Y - 1.5, Y - 1.);
+            const float z = randBetween(Z / 2.f - Z / 3.f, Z / 2.f + Z / 3.f);
+            p.position = Vector3f(x, y, z);
+            p.velocity = Vector3f(0, 0, 0);
+            p.opacity = 1.f;
+            p.lifeTime = 5.f;
+            ink.push_back(p);
+        }
+        drops.push_back(ink);
+    }
+}
+
+// initFromFile (src/system.cpp:117-148): one particle per line, "x y z vx vy vz" separated by single spaces.
+std::vector<Particle> from_file(const std::string& path) {
+    std::ifstream pf(path);
+    if (!pf.is_open()) throw std::runtime_error("PART_FILE cannot be opened: " + path);
+    std::vector<Particle> ink;
+    std::string line;
+    while (std::getline(pf, line)) {
+        float vals[6] = {0, 0, 0, 0, 0, 0};
+        std::stringstream s(line);
+        std::string tok;
+        int idx = 0;
+        while (idx < 6 && std::getline(s, tok, ' ')) vals[idx++] = std::stof(tok);
+        Particle p;
+        p.position = Vector3f(vals[0], vals[1], vals[2]);
+        p.velocity = Vector3f(vals[3], vals[4], vals[5]);
+        p.opacity = 1.f;
+        p.lifeTime = 5.f;
+        ink.push_back(p);
+    }
+    return ink;
+}
+
+// emitParticleHemisphere (src/inkSolver.cpp:11-42).  The reference rotates by AngleAxisf(pi, (n + up).normalized()) with
+// n = -up, i.e. about the ZERO axis: Eigen leaves a zero vector un-normalised and the rotation matrix degenerates to
+// cos(pi) * I = -I, so velocity = -(x, y, z) and position = ceiling centre + radius * velocity.  The float
+// loop counters (73 x 37 iterations per radius) are kept as float accumulations.
+void hemisphere(int X, int Y, int Z, float radius, std::vector<Particle>& out) {
+    // double-precision M_PI expressions rounded to float once, exactly as the reference writes them
+    const float fraction = M_PI / 36.f;
+    const float twoPi = M_PI * 2.f;
+    const float c = std::cos((float)M_PI);   // -1: the only surviving term of the degenerate rotation
+    for (float i = 0; i < twoPi; i += fraction) {
+        for (float j = 0; j < M_PI; j += fraction) {
+            const float x = radius * std::sin(j) * std::sin(i);
+            const float y = radius * std::cos(j);
+            const float z = radius * std::sin(j) * std::cos(i);
+            Particle p;
+            // rows of the degenerate rotation matrix c*I applied the way a 3x3 product is: (c*x + 0*y) + 0*z — this keeps
+            // the sign of zero identical to the reference (-0 + 0 = +0), so the .ply bytes agree
+            const float zf = 0.f;
+            p.velocity = Vector3f((c * x + zf * y) + zf * z, (zf * x + c * y) + zf * z, (zf * x + zf * y) + c * z);
+            p.position = Vector3f(X / 2.f, Y - 0.1f, Z / 2.f) + radius * p.velocity;
+            p.opacity = 1.f;
+            p.lifeTime = 5.f;
+            out.push_back(p);
+        }
+    }
+}
+
+void emitter_scene(int X, int Y, int Z, std::vector<Particle>& out) {
+    for (float i = 0; i < 2 * M_PI; i += (M_PI / 60.f)) hemisphere(X, Y, Z, i, out);
+}
+
+}  // namespace inkseed
+
+// C hooks for the CPU-side tests (ctypes): the emitter scene as flat arrays
+extern "C" long inkhost_emitter_scene(int X, int Y, int Z, float* pos, float* vel, long cap) {
+    std::vector<Particle> out;
+    inkseed::emitter_scene(X, Y, Z, out);
+    const long n = (long)out.size();
+    for (long i = 0; i < n && i < cap; ++i)
+        for (int a = 0; a < 3; ++a) { pos[3 * i + a] = out[i].position[a]; vel[3 * i + a] = out[i].velocity[a]; }
+    return n;
+}

@@ -1,0 +1,156 @@
+// system.cpp — the reference's `System` (src/system.{h,cpp}, src/inkSolver.cpp:5-9) as a thin owner of an ink_ctx.
+// All per-timestep arithmetic runs in libinkb200.so on the GPU; this file only seeds particles on the host the way
+// System::init does, forwards solve(), and refreshes the host mirrors that the reference's getters expose.
+#include "system.h"
+
+#include <cmath>
+#include <cstdlib>
+#include <fstream>
+#include <sstream>
+#include <stdexcept>
+
+#include "../../include/ink_capi.h"
+#include "seeding.h"
+
+using Eigen::Vector3f;
+using Eigen::Vector3i;
+
+System::System() {}
+
+System::~System() {
+    if (m_ctx) ink_destroy(m_ctx);
+}
+
+void System::fail(const char* what) const {
+    throw std::runtime_error(std::string(what) + ": " + ink_last_error(m_ctx));
+}
+
+// System::init (src/system.cpp:10-26): grid first (zero velocity; no LU factorisation to set up — the pressure solve
+// is matrix-free), then the particles.
+void System::init() {
+    ink_params p;
+    ink_default_params(&p);
+    p.X = WATERGRID_X; p.Y = WATERGRID_Y; p.Z = WATERGRID_Z;
+    p.cell_dim = CELL_DIM; p.density = DENSITY; p.k_vort = K_VORT; p.viscosity = VISCOSITY; p.p_atm = ATMOSPHERIC_PRESSURE;
+    p.gravity[0] = gravity[0]; p.gravity[1] = gravity[1]; p.gravity[2] = gravity[2];
+    p.k_cfl = K_CFL; p.dt_min = MIN_TIMESTEP; p.dt_max = MAX_TIMESTEP; p.buffer_size = BUFFER_SIZE;
+    if (const char* e = std::getenv("INK_PRECISION")) p.precision = std::atoi(e);
+    if (const char* e = std::getenv("INK_ARITH")) p.arith = std::string(e) == "fast" ? INK_ARITH_FAST : INK_ARITH_STRICT;
+    if (const char* e = std::getenv("INK_DEVICE")) p.device = std::atoi(e);
+    if (ink_create(&p, &m_ctx) != 0) throw std::runtime_error(std::string("ink_create: ") + ink_last_error(nullptr));
+
+    if (PART_FILE != "") {
+        initFromFile();
+    } else if (INK_SEED_BOX) {
+        initParticles();
+    } else {
+        std::vector<Particle> ink;
+        ink.reserve(400000);
+        m_ink.push_back(ink);
+        for (float i = 0; i < 2 * M_PI; i += (M_PI / 60.f)) emitParticleHemisphere(i);
+    }
+    uploadInk();
+}
+
+void System::uploadInk() {
+    std::vector<float> pos, vel;
+    for (size_t d = 0; d < m_ink.size(); ++d) {
+        const std::vector<Particle>& ink = m_ink[d];
+        pos.resize(ink.size() * 3);
+        vel.resize(ink.size() * 3);
+        for (size_t i = 0; i < ink.size(); ++i)
+            for (int a = 0; a < 3; ++a) { pos[3 * i + a] = ink[i].position[a]; vel[3 * i + a] = ink[i].velocity[a]; }
+        if (ink_set_particles(m_ctx, (int)d, pos.data(), vel.data(), (int64_t)ink.size(), 32) != 0) fail("ink_set_particles");
+    }
+    m_inkStale = false;
+}
+
+// ---- particle seeding (seeding.cpp holds the arithmetic; these are the reference's member names) ---------------------
+void System::initParticles() { inkseed::box(WATERGRID_X, WATERGRID_Y, WATERGRID_Z, NUM_PARTICLES, m_ink); }
+void System::initFromFile() { m_ink.push_back(inkseed::from_file(PART_FILE)); }
+void System::emitParticleHemisphere(float radius) { inkseed::hemisphere(WATERGRID_X, WATERGRID_Y, WATERGRID_Z, radius, m_ink[0]); }
+
+// ---- the hot path ----------------------------------------------------------------------------------------------------
+double System::solve(double timeToNextRender) {
+    double dt = 0;
+    if (ink_step(m_ctx, timeToNextRender, &dt) != 0) fail("ink_step");
+    m_inkStale = true;
+    return dt;
+}
+
+// ---- getters -----------------------------------------------------------------------------------------------------------
+int System::numDrops() const { return ink_num_drops(m_ctx); }
+long long System::numParticles(int drop) const { return ink_num_particles(m_ctx, drop); }
+void System::copyPositions(int drop, float* xyz) {
+    if (ink_get_particles(m_ctx, drop, xyz, nullptr, 32) != 0) fail("ink_get_particles");
+}
+void System::copyVelocityField(float* u, float* v, float* w) {
+    if (ink_get_field(m_ctx, INK_FIELD_CURR, u, v, w, 32) != 0) fail("ink_get_field");
+}
+
+const std::vector<std::vector<Particle>>& System::getInkParticles() {
+    if (!m_inkStale) return m_ink;
+    std::vector<float> pos, vel;
+    for (size_t d = 0; d < m_ink.size(); ++d) {
+        std::vector<Particle>& ink = m_ink[d];
+        pos.resize(ink.size() * 3);
+        vel.resize(ink.size() * 3);
+        if (ink.empty()) continue;
+        if (ink_get_particles(m_ctx, (int)d, pos.data(), vel.data(), 32) != 0) fail("ink_get_particles");
+        for (size_t i = 0; i < ink.size(); ++i) {
+            ink[i].position = Vector3f(pos[3 * i], pos[3 * i + 1], pos[3 * i + 2]);
+            ink[i].velocity = Vector3f(vel[3 * i], vel[3 * i + 1], vel[3 * i + 2]);
+        }
+    }
+    m_inkStale = false;
+    return m_ink;
+}
+
+// The reference returns its whole hash map BY VALUE (src/system.cpp:155-157); so does this, rebuilt from the dense
+// device arrays.  old == curr between steps (src/waterSolver.cpp:92-95); curl is the last confinement pass's.
+const std::unordered_map<Vector3i, Cell, hash_func> System::getWaterGrid() {
+    const size_t n = (size_t)WATERGRID_X * WATERGRID_Y * WATERGRID_Z;
+    std::vector<float> u(n), v(n), w(n), cx(n), cy(n), cz(n);
+    if (ink_get_field(m_ctx, INK_FIELD_CURR, u.data(), v.data(), w.data(), 32) != 0) fail("ink_get_field");
+    if (ink_get_field(m_ctx, INK_FIELD_CURL, cx.data(), cy.data(), cz.data(), 32) != 0) fail("ink_get_field");
+    m_waterGrid.clear();
+    m_waterGrid.reserve(n);
+    for (int i = 0; i < WATERGRID_X; ++i)
+        for (int j = 0; j < WATERGRID_Y; ++j)
+            for (int k = 0; k < WATERGRID_Z; ++k) {
+                const size_t c = ((size_t)i * WATERGRID_Y + j) * WATERGRID_Z + k;
+                Cell cell;
+                cell.oldVelocity = cell.currVelocity = Vector3f(u[c], v[c], w[c]);
+                cell.curl = Vector3f(cx[c], cy[c], cz[c]);
+                const int nb[6][3] = {{i + 1, j, k}, {i - 1, j, k}, {i, j + 1, k}, {i, j - 1, k}, {i, j, k + 1}, {i, j, k - 1}};
+                for (const auto& q : nb)
+                    if (q[0] >= 0 && q[0] < WATERGRID_X && q[1] >= 0 && q[1] < WATERGRID_Y && q[2] >= 0 && q[2] < WATERGRID_Z)
+                        cell.neighbors.push_back(Vector3i(q[0], q[1], q[2]));
+                m_waterGrid.insert({Vector3i(i, j, k), cell});
+            }
+    return m_waterGrid;
+}
+
+// checkNanAndInf (src/systemHelpers.cpp:212-241): assert-only in the reference; here it throws.
+void System::checkNanAndInf() {
+    const size_t n = (size_t)WATERGRID_X * WATERGRID_Y * WATERGRID_Z;
+    std::vector<float> f[3] = {std::vector<float>(n), std::vector<float>(n), std::vector<float>(n)};
+    copyVelocityField(f[0].data(), f[1].data(), f[2].data());
+    for (const auto& a : f)
+        for (float x : a)
+            if (!std::isfinite(x)) throw std::runtime_error("checkNanAndInf: non-finite grid velocity");
+    for (const auto& ink : getInkParticles())
+        for (const Particle& p : ink)
+            for (int a = 0; a < 3; ++a)
+                if (!std::isfinite(p.position[a]) || !std::isfinite(p.velocity[a])) throw std::runtime_error("checkNanAndInf: non-finite particle");
+}
+
+std::ostream& operator<<(std::ostream& strm, const Cell& obj) {
+    return strm << "Cell(old " << obj.oldVelocity << ", curr " << obj.currVelocity << ", curl " << obj.curl << ")";
+}
+std::ostream& operator<<(std::ostream& strm, const Particle& obj) {
+    return strm << "Particle(pos " << obj.position << ", vel " << obj.velocity << ", opacity " << obj.opacity << ", life " << obj.lifeTime << ")";
+}
+std::ostream& operator<<(std::ostream& strm, const System& obj) {
+    return strm << "System(" << WATERGRID_X << "x" << WATERGRID_Y << "x" << WATERGRID_Z << ", " << obj.m_ink.size() << " drops)";
+}

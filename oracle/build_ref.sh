@@ -30,7 +30,7 @@ cp "$REF"/src/system.h "$REF"/src/system.cpp "$REF"/src/systemHelpers.cpp "$REF"
    "$REF"/src/inkSolver.cpp "$REF"/src/inkSim.h "$REF"/src/inkSim.cpp "$TMP"/
 sed -i -E 's/^const int (WATERGRID_[XYZ]) *=/inline int \1 =/' "$TMP/system.h"
 grep -c '^inline int WATERGRID_' "$TMP/system.h" | grep -qx 3 || { echo "build_ref: sed did not patch 3 lines"; exit 1; }
-g++ -std=c++20 -O2 -DNDEBUG -ffp-contract=off -fPIC -shared -w \
+g++ -std=c++20 -O2 -DNDEBUG -ffp-contract=off -fPIC -shared -w -Wl,-Bsymbolic \
     -I"$REF" -I"$TMP" \
     "$HERE/ref_shim.cpp" "$TMP/system.cpp" "$TMP/systemHelpers.cpp" "$TMP/waterSolver.cpp" \
     "$TMP/inkSolver.cpp" "$TMP/inkSim.cpp" \

@@ -35,7 +35,7 @@ def main():
         if not ok:
             failures.append(f"rank {rank}: {name} {info}")
 
-    for dims, npart in (((16, 40, 12), 20000), ((32, 64, 32), 200000)):
+    for dims, npart in (((16, 5 * world, 12), 5000), ((16, 40, 12), 20000), ((32, 64, 32), 200000)):
         u, v, w = util.rand_field(dims, 11, scale=0.5)
         part = util.uniform_particles(dims, npart, 12)
         lo, hi = shard_range(npart, rank, world)
