@@ -121,6 +121,15 @@ def cpu_port_sample(dims, pos, steps, warm_state=None):
     return dt, os.cpu_count()
 
 
+def workload_config(args, cfg, dims, n, world):
+    """The `config` object both arms print (the reference arm runs a bounded sample of it and says which)."""
+    return {"workload": f"{args.config}: {n} particles ({cfg['cloud']}, unsorted input), {dims[0]}x{dims[1]}x{dims[2]} MAC grid, "
+                        f"full System::solve per step", "arith": args.arith, "cg_rtol": args.cg_rtol,
+            "resort_interval": args.resort, "precond": args.precond,
+            "sharding": "single GPU" if world == 1 else f"{world} y-slabs of {dims[1] // world} rows, particles by index; NCCL",
+            "l2": "inputs larger than L2 (per GPU: particle arrays 360 MB + 15 grid vectors of 16.8 MB; L2 = 126 MB)"}
+
+
 def run_reference_arm(args, cfg, rank, world):
     """--impl reference: the CPU implementation on the host cores.  The compiled reference (hash-map grid + SparseLU)
     cannot run grids beyond ~32x64x32, so for c3/c4 the OpenMP oracle port stands in (kind: "port")."""
@@ -147,12 +156,16 @@ def run_reference_arm(args, cfg, rank, world):
         T.solve(RENDER_DT)
     sec = (time.perf_counter() - t0) / args.steps
     val = sample_n / sec
-    sample = f"{args.steps} System::solve steps, grid {dims[0]}x{dims[1]}x{dims[2]}, {sample_n} particles ({cfg['cloud']})"
+    sample = (f"{args.steps} System::solve steps of one GPU's share of the workload: grid {dims[0]}x{dims[1]}x{dims[2]}, {sample_n} particles "
+              f"({cfg['cloud']}); {'compiled reference, 1 thread (it has no threading)' if use_ref else 'OpenMP oracle port, exact DST Poisson solve'}")
+    wdims, wn = dims, n
+    if world > 1 and not args.strong:
+        wdims, wn = (dims[0], dims[1] * world, dims[2]), n * world
     line = {
         "impl": "reference", "metric": "particle_rk2_updates_per_s", "value": val, "unit": "particle-updates/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": args.config, "grid": list(dims), "particles": sample_n, "cloud": cfg["cloud"]},
+        "config": workload_config(args, cfg, wdims, wn, world),
         "mac_cell_steps_per_s": dims[0] * dims[1] * dims[2] / sec,
         "cpu_baseline": {"value": val, "unit": "particle-updates/s", "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": val, "unit": "particle-updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -356,11 +369,7 @@ def main():
         "warmup": max(3, args.warmup), "ms_per_step": ms_step, "higher_is_better": True,
         "scaling": "strong" if (world > 1 and args.strong) else "weak", "vs_baseline": None,
         "dtype": args.dtype, "data": "synthetic",
-        "config": {"workload": f"{args.config}: {n} particles ({cfg['cloud']}, unsorted input), {dims[0]}x{dims[1]}x{dims[2]} MAC grid, "
-                               f"full System::solve per step", "arith": args.arith, "cg_rtol": args.cg_rtol,
-                   "resort_interval": args.resort, "precond": args.precond,
-                   "sharding": "single GPU" if world == 1 else f"{world} y-slabs of {dims[1] // world} rows, particles by index; NCCL",
-                   "l2": "inputs larger than L2 (per GPU: particle arrays 360 MB + 15 grid vectors of 16.8 MB; L2 = 126 MB)"},
+        "config": workload_config(args, cfg, dims, n, world),
         "mac_cell_steps_per_s": ncell / (ms_step * 1e-3),
         "mac_only_cell_steps_per_s": ncell / (water_ms * 1e-3) if water_ms > 0 else None,
         "particles_only_updates_per_s": n / (part_ms * 1e-3) if part_ms > 0 else None,
