@@ -11,6 +11,9 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+// host+device helpers: the multigrid level operators are also run on the HOST by tests/mg_host_harness.cu
+#define INK_HD __host__ __device__ __forceinline__
+
 namespace ink {
 
 struct Grid {

@@ -40,11 +40,11 @@ struct MgLevelPtrs {
     Real s;              // operator scale 2^l
 };
 
-__device__ __forceinline__ long long mg_idx(const MgDims& d, int i, int j, int k) { return ((long long)j * d.X + i) * d.Z + k; }
+INK_HD long long mg_idx(const MgDims& d, int i, int j, int k) { return ((long long)j * d.X + i) * d.Z + k; }
 
 // sum of the in-grid (and in-slab) face neighbours of cell (i,j,k)
 template <class Real>
-__device__ __forceinline__ Real mg_nbr_sum(const MgDims& d, const Real* __restrict__ x, int i, int j, int k, long long c) {
+INK_HD Real mg_nbr_sum(const MgDims& d, const Real* __restrict__ x, int i, int j, int k, long long c) {
     const long long sx = d.Z, sy = (long long)d.X * d.Z;
     Real a = Real(0);
     if (i + 1 < d.X) a += x[c + sx];
@@ -61,7 +61,7 @@ __device__ __forceinline__ Real mg_nbr_sum(const MgDims& d, const Real* __restri
 struct MgIter {
     unsigned int t, tot, nth;
     int i, jl, k, di, dj, dk, X, Z;
-    __device__ __forceinline__ MgIter(const MgDims& d, unsigned int tid, unsigned int nthreads) {
+    INK_HD MgIter(const MgDims& d, unsigned int tid, unsigned int nthreads) {
         X = d.X; Z = d.Z; nth = nthreads; t = tid;
         tot = (unsigned int)(d.j1 - d.j0) * (unsigned int)d.X * (unsigned int)d.Z;
         unsigned int row = tid / (unsigned int)Z;
@@ -73,8 +73,8 @@ struct MgIter {
         dj = (int)(row / (unsigned int)X);
         di = (int)(row - (unsigned int)dj * (unsigned int)X);
     }
-    __device__ __forceinline__ bool ok() const { return t < tot; }
-    __device__ __forceinline__ void next() {
+    INK_HD bool ok() const { return t < tot; }
+    INK_HD void next() {
         t += nth;
         k += dk; if (k >= Z) { k -= Z; ++i; }
         i += di; if (i >= X) { i -= X; ++jl; }
@@ -101,7 +101,7 @@ __device__ __forceinline__ void mg_presmooth(const MgDims& d, Real s, const Real
 
 // one Jacobi sweep xo = xi + c (r - s L xi); returns this thread's partial of <r, xo> (used by the final sweep)
 template <class Real>
-__device__ __forceinline__ double mg_smooth(const MgDims& d, Real s, const Real* __restrict__ r, const Real* __restrict__ xi, Real* __restrict__ xo,
+INK_HD double mg_smooth(const MgDims& d, Real s, const Real* __restrict__ r, const Real* __restrict__ xi, Real* __restrict__ xo,
                                             long long tid, long long nth, int dj0 = 0, int dj1 = 0x7fffffff) {
     const Real cj = Real(kMgOmega) / (Real(6) * s);
     double acc = 0;

@@ -1,0 +1,297 @@
+// mg_tri.cuh — second-generation multigrid preconditioner for the matrix-free CG pressure solve (cg.cuh):
+// V(1,1) cycle with cell-centred TRILINEAR prolongation P and full-weighting restriction R = P^T.
+//
+// Why (scripts/mg_proto.py, numpy): the piecewise-constant transfer of mg.cuh needs V(2,2) to reach ~13-16 CG
+// iterations; trilinear transfer reaches 10 with V(1,1) (8 with V(2,2)) at 64x128x64, size-independent, and V(1,1)
+// needs far fewer passes over a level:
+//      down : res = r - s M (c r) = r - (omega/6) M r                      (the sweep from zero is never stored)
+//             r_{l+1} = P^T res
+//      up   : x' = c r + P e ;  z = x' + c (r - s M x') = c r + (1-omega) x' + (omega/6) N x'
+//                                                                         (x' is never stored: ONE pass r, e -> z)
+// with M x = 6x - N x, N = sum of the in-grid (in-slab) face neighbours, c = omega / (6 s_l), s_l = 2^l.
+// Fine-level traffic per CG iteration: 8 (res) + 4.5 (restrict) + 8.5 (up) = 21 B/cell instead of 46 B/cell.
+//
+// 1-D transfer (tensor product in 3-D): fine cell f has parent c = f >> 1 and second donor o = c + (f odd ? +1 : -1);
+// P[f, c] = 3/4, P[f, o] = 1/4, donors outside the coarse grid (or slab) are dropped (zero Dirichlet ghost, like
+// the ghost pressure of the reference's matrix, src/waterSolver.cpp:240-261).  The cycle is a fixed symmetric
+// positive-definite operator: R = P^T exactly (same masks), Jacobi is self-adjoint, coarsest level = a fixed
+// polynomial in the level operator (kMgCoarsestSweeps damped-Jacobi sweeps from zero).
+//
+// The level operators are (thread id, thread count)-strided INK_HD functions: the global-memory kernels, the
+// shared-memory tail and the HOST harness (tests/mg_host_harness.cu, checked against the numpy prototype without a
+// GPU) all execute the same code.
+#pragma once
+#include "mg.cuh"
+#include "mg_vec.cuh"
+
+namespace ink {
+
+constexpr int kMg3CoarsestCells = 1024;   // stop coarsening at <= this many cells (prototype: same iteration count as 16)
+
+// res = r - (omega/6) M r
+template <class Real>
+INK_HD void mg3_residual(const MgDims& d, const Real* __restrict__ r, Real* __restrict__ res, long long tid, long long nth) {
+    const Real w6 = Real(kMgOmega) / Real(6);
+    INK_MG_CELL_LOOP(d, tid, nth) {
+        INK_MG_DECODE(d)
+        const Real rc = r[c];
+        res[c] = rc - w6 * (Real(6) * rc - mg_nbr_sum(d, r, i, j, k, c));
+    }
+}
+
+// rc = P^T res : coarse cell (I,J,K) gathers the 4x4x4 fine cells 2I-1..2I+2 (weights 1/4, 3/4, 3/4, 1/4 per axis)
+template <class Real>
+INK_HD void mg3_restrict(const MgDims& df, const MgDims& dc, const Real* __restrict__ res, Real* __restrict__ rc, long long tid, long long nth) {
+    INK_MG_CELL_LOOP(dc, tid, nth) {
+        INK_MG_DECODE(dc)
+        Real acc = Real(0);
+#pragma unroll
+        for (int n = 0; n < 4; ++n) {
+            const int fj = 2 * j - 1 + n;
+            if (fj < df.j0 || fj >= df.j1) continue;
+            const Real wy = (n == 1 || n == 2) ? Real(0.75) : Real(0.25);
+#pragma unroll
+            for (int l = 0; l < 4; ++l) {
+                const int fi = 2 * i - 1 + l;
+                if (fi < 0 || fi >= df.X) continue;
+                const Real wxy = wy * ((l == 1 || l == 2) ? Real(0.75) : Real(0.25));
+                const long long row = mg_idx(df, fi, fj, 0);
+                Real a = Real(0);
+#pragma unroll
+                for (int m = 0; m < 4; ++m) {
+                    const int fk = 2 * k - 1 + m;
+                    if (fk < 0 || fk >= df.Z) continue;
+                    a += ((m == 1 || m == 2) ? Real(0.75) : Real(0.25)) * res[row + fk];
+                }
+                acc += wxy * a;
+            }
+        }
+        rc[c] = acc;
+    }
+}
+
+// the four fine positions 2c-1, 2c, 2c+1, 2c+2 interpolated from coarse c-1, c, c+1
+template <class Real>
+INK_HD void mg3_interp4(Real v0, Real v1, Real v2, Real (&o)[4]) {
+    o[0] = Real(0.75) * v0 + Real(0.25) * v1;
+    o[1] = Real(0.75) * v1 + Real(0.25) * v0;
+    o[2] = Real(0.75) * v1 + Real(0.25) * v2;
+    o[3] = Real(0.75) * v2 + Real(0.25) * v1;
+}
+
+// z = c r + (1-omega) x' + (omega/6) N x',  x' = c r + P e.  One thread per COARSE cell (I,J,K) = the 2x2x2 fine block
+// (2I+a, 2J+b, 2K+q): the 27 coarse values around it give P e on the 4x4x4 fine cells 2I-1..2I+2 (separable
+// interpolation in registers); x' is formed there (0 outside the grid / slab, which is exactly "N sums in-grid neighbours
+// only") and the 8 outputs follow.  Per fine cell: 4 loads of r + 3.4 loads of e instead of 7 x (1 + 8).
+// Returns this thread's partial of <r, z> over rows [dj0, dj1).
+template <class Real>
+INK_HD double mg3_up(const MgDims& df, const MgDims& dc, Real s, const Real* __restrict__ r, const Real* __restrict__ e, Real* __restrict__ z,
+                     long long tid, long long nth, int dj0 = 0, int dj1 = 0x7fffffff) {
+    const Real cj = Real(kMgOmega) / (Real(6) * s), a0 = Real(1) - Real(kMgOmega), a1 = Real(kMgOmega) / Real(6);
+    double acc = 0;
+    INK_MG_CELL_LOOP(dc, tid, nth) {
+        const int I = it_.i, K = it_.k, J = dc.j0 + it_.jl;
+        // P e on the 4x4x4 block: z, then y, then x
+        Real tz[3][3][4];
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            const int ii = I + a - 1;
+            const bool vx = (ii >= 0) && (ii < dc.X);
+#pragma unroll
+            for (int b = 0; b < 3; ++b) {
+                const int jj = J + b - 1;
+                const bool vxy = vx && (jj >= dc.j0) && (jj < dc.j1);
+                Real ev[3];
+#pragma unroll
+                for (int q = 0; q < 3; ++q) {
+                    const int kk = K + q - 1;
+                    ev[q] = (vxy && kk >= 0 && kk < dc.Z) ? e[mg_idx(dc, ii, jj, kk)] : Real(0);
+                }
+                mg3_interp4(ev[0], ev[1], ev[2], tz[a][b]);
+            }
+        }
+        Real ty[3][4][4];   // [a][n][m]
+#pragma unroll
+        for (int a = 0; a < 3; ++a)
+#pragma unroll
+            for (int m = 0; m < 4; ++m) {
+                Real o[4];
+                mg3_interp4(tz[a][0][m], tz[a][1][m], tz[a][2][m], o);
+#pragma unroll
+                for (int n = 0; n < 4; ++n) ty[a][n][m] = o[n];
+            }
+        Real xp[4][4][4];   // [l][n][m] <-> fine (2I-1+l, 2J-1+n, 2K-1+m)
+        Real rin[2][2][2];
+#pragma unroll
+        for (int n = 0; n < 4; ++n)
+#pragma unroll
+            for (int m = 0; m < 4; ++m) {
+                Real o[4];
+                mg3_interp4(ty[0][n][m], ty[1][n][m], ty[2][n][m], o);
+#pragma unroll
+                for (int l = 0; l < 4; ++l) xp[l][n][m] = o[l];
+            }
+        // x' = c r + P e where the fine cell exists, else 0 (only the 8 block cells and their 24 face neighbours are used)
+#pragma unroll
+        for (int l = 0; l < 4; ++l) {
+            const int fi = 2 * I - 1 + l;
+            const bool vx = (fi >= 0) && (fi < df.X);
+#pragma unroll
+            for (int n = 0; n < 4; ++n) {
+                const int fj = 2 * J - 1 + n;
+                const bool vxy = vx && (fj >= df.j0) && (fj < df.j1);
+#pragma unroll
+                for (int m = 0; m < 4; ++m) {
+                    const int outer = (l == 0 || l == 3) + (n == 0 || n == 3) + (m == 0 || m == 3);
+                    if (outer >= 2) continue;   // edges / corners of the 4x4x4 block are not face neighbours of the 2x2x2 block
+                    const int fk = 2 * K - 1 + m;
+                    Real v = Real(0);
+                    if (vxy && fk >= 0 && fk < df.Z) {
+                        const Real rr = r[mg_idx(df, fi, fj, fk)];
+                        v = cj * rr + xp[l][n][m];
+                        if (outer == 0) rin[l - 1][n - 1][m - 1] = rr;
+                    }
+                    xp[l][n][m] = v;
+                }
+            }
+        }
+#pragma unroll
+        for (int l = 1; l < 3; ++l) {
+            const int fi = 2 * I - 1 + l;
+            if (fi >= df.X) continue;
+#pragma unroll
+            for (int n = 1; n < 3; ++n) {
+                const int fj = 2 * J - 1 + n;
+                if (fj < df.j0 || fj >= df.j1) continue;
+#pragma unroll
+                for (int m = 1; m < 3; ++m) {
+                    const int fk = 2 * K - 1 + m;
+                    if (fk >= df.Z) continue;
+                    const Real nb = (xp[l - 1][n][m] + xp[l + 1][n][m]) + (xp[l][n - 1][m] + xp[l][n + 1][m]) + (xp[l][n][m - 1] + xp[l][n][m + 1]);
+                    const Real rr = rin[l - 1][n - 1][m - 1];
+                    const Real v = cj * rr + a0 * xp[l][n][m] + a1 * nb;
+                    z[mg_idx(df, fi, fj, fk)] = v;
+                    if (fj >= dj0 && fj < dj1) acc += (double)rr * (double)v;
+                }
+            }
+        }
+    }
+    return acc;
+}
+
+#ifdef __CUDACC__
+// ---- global-memory kernels ---------------------------------------------------------------------------------------
+template <class Real>
+__global__ void __launch_bounds__(256) k_mg3_residual(const CgScal* S, MgDims d, const Real* __restrict__ r, Real* __restrict__ res) {
+    if (S->done) return;
+    mg3_residual<Real>(d, r, res, (long long)blockIdx.x * blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x);
+}
+// Z % 4 == 0: one thread per 4 z-consecutive cells, 128-bit accesses (same arithmetic per cell)
+template <class Real>
+__global__ void __launch_bounds__(256) k_mg3_residual_v4(const CgScal* S, MgDims d, const Real* __restrict__ r, Real* __restrict__ res) {
+    if (S->done) return;
+    const Real w6 = Real(kMgOmega) / Real(6);
+    int i, j, k; long long c;
+    for (unsigned int t = blockIdx.x * blockDim.x + threadIdx.x; mg_vec_cell(d, t, i, j, k, c); t += gridDim.x * blockDim.x) {
+        const P4<Real> rc = ldp<Real, 4>(r + c);
+        Real L[4];
+        mg_lap4<Real>(d, r, rc, i, j, k, c, L);
+        P4<Real> o;
+#pragma unroll
+        for (int a = 0; a < 4; ++a) o.a[a] = rc.a[a] - w6 * L[a];
+        stp<Real, 4>(res + c, o);
+    }
+}
+template <class Real>
+__global__ void __launch_bounds__(256) k_mg3_restrict(const CgScal* S, MgDims df, MgDims dc, const Real* __restrict__ res, Real* __restrict__ rc) {
+    if (S->done) return;
+    mg3_restrict<Real>(df, dc, res, rc, (long long)blockIdx.x * blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x);
+}
+// FINAL: level 0 — also produces <r, z> for CG (rz_old <- rz, rz <- <r,z>)
+template <class Real, bool FINAL>
+__global__ void __launch_bounds__(256) k_mg3_up(CgScal* S, MgDims df, MgDims dc, Real s, const Real* __restrict__ r, const Real* __restrict__ e,
+                                                Real* __restrict__ z, int dj0, int dj1) {
+    if (S->done) return;
+    const double acc = mg3_up<Real>(df, dc, s, r, e, z, (long long)blockIdx.x * blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x, dj0, dj1);
+    if (FINAL) {
+        double tot;
+        if (block_sum_last(acc, S, 0, tot)) {
+            if (threadIdx.x == 0) { if (S->dist) S->loc[2] = tot; else { S->rz_old = S->rz; S->rz = tot; } }
+        }
+    }
+}
+
+// ---- shared-memory tail: all levels from `lt` down in ONE block (MgTailArgs of mg.cuh; 3 arrays per level) ----------
+template <class Real>
+__global__ void __launch_bounds__(kMgTailThreads) k_mg3_tail(CgScal* S, MgTailArgs A, const Real* __restrict__ rin, Real* __restrict__ xout) {
+    if (S->done) return;
+    extern __shared__ __align__(16) unsigned char mg_smem_raw[];
+    Real* sm = reinterpret_cast<Real*>(mg_smem_raw);
+    const long long tid = threadIdx.x, nth = blockDim.x;
+    Real *xx[kMgMaxLevels], *tmp[kMgMaxLevels], *rr[kMgMaxLevels];   // xx: level result e; tmp: residual / Jacobi ping-pong
+    {
+        Real* p = sm;
+        for (int q = 0; q < A.nlev; ++q) {
+            const long long n = (long long)A.d[q].X * A.d[q].Y * A.d[q].Z;
+            xx[q] = p; tmp[q] = p + n; rr[q] = p + 2 * n;
+            p += 3 * n;
+        }
+    }
+    const long long n0 = (long long)A.d[0].X * A.d[0].Y * A.d[0].Z;
+    for (long long c = tid; c < n0; c += nth) rr[0][c] = rin[c];
+    __syncthreads();
+    Real s = (Real)A.s0;
+    for (int q = 0; q + 1 < A.nlev; ++q) {   // down
+        mg3_residual<Real>(A.d[q], rr[q], tmp[q], tid, nth);
+        __syncthreads();
+        mg3_restrict<Real>(A.d[q], A.d[q + 1], tmp[q], rr[q + 1], tid, nth);
+        __syncthreads();
+        s *= Real(2);
+    }
+    const Real* ecoarse;
+    {   // coarsest: kMgCoarsestSweeps damped-Jacobi sweeps from zero
+        const int q = A.nlev - 1;
+        const long long n = (long long)A.d[q].X * A.d[q].Y * A.d[q].Z;
+        const Real cj = Real(kMgOmega) / (Real(6) * s);
+        Real *a = xx[q], *b = tmp[q];
+        for (long long c = tid; c < n; c += nth) a[c] = cj * rr[q][c];
+        __syncthreads();
+        for (int t = 1; t < kMgCoarsestSweeps; ++t) {
+            mg_smooth<Real>(A.d[q], s, rr[q], a, b, tid, nth);
+            __syncthreads();
+            Real* w = a; a = b; b = w;
+        }
+        ecoarse = a;
+    }
+    for (int q = A.nlev - 2; q >= 1; --q) {   // up
+        s *= Real(0.5);
+        mg3_up<Real>(A.d[q], A.d[q + 1], s, rr[q], ecoarse, xx[q], tid, nth);
+        __syncthreads();
+        ecoarse = xx[q];
+    }
+    double acc = 0;
+    if (A.nlev > 1) {
+        s *= Real(0.5);
+        acc = mg3_up<Real>(A.d[0], A.d[1], s, rr[0], ecoarse, xout, tid, nth, A.dj0, A.dj1);
+    } else
+        for (long long c = tid; c < n0; c += nth) {
+            const Real v = ecoarse[c];
+            xout[c] = v;
+            const int jrow = (int)(c / ((long long)A.d[0].X * A.d[0].Z));
+            if (jrow >= A.dj0 && jrow < A.dj1) acc += (double)rr[0][c] * (double)v;
+        }
+    if (A.final_dot) {
+        __shared__ double red[kMgTailThreads / 32];
+        acc = warp_sum(acc);
+        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double t = 0;
+            for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += red[w];
+            if (S->dist) S->loc[2] = t; else { S->rz_old = S->rz; S->rz = t; }
+        }
+    }
+}
+#endif  // __CUDACC__
+
+}  // namespace ink
