@@ -183,7 +183,7 @@ def main():
     ap.add_argument("--particles", type=int, default=None)
     ap.add_argument("--arith", default="fast", choices=["strict", "fast"],
                     help="fast: FMA lerps in the particle sampler (<= 1e-6 relative vs the reference, tested); strict: bit-exact")
-    ap.add_argument("--precond", default="mg", choices=["mg", "none"])
+    ap.add_argument("--precond", default="mg", choices=["mg", "mg_const", "none"])
     ap.add_argument("--strong", action="store_true", help="N > 1: keep the total problem fixed instead of the per-GPU problem")
     ap.add_argument("--dtype", default="f32", choices=["f32", "f64"])
     ap.add_argument("--cg-rtol", type=float, default=1e-6)
@@ -343,10 +343,10 @@ def main():
             "alg_bytes_per_launch": alg_k8, "launch_ms": part_ms,
             "note": "issue/L1-gather bound, not HBM bound: 48 trilinear corner gathers per particle (profiles/)"}
     # the pressure phase as a whole (CG pair + V-cycle kernels): bytes the ALGORITHM needs per iteration on the fine level
-    # (CG 10 + V-cycle 11.5 vector passes) vs time; launch-latency-bound coarse levels count against it
+    # (CG 10 + V-cycle 5.25 [trilinear V(1,1)] or 11.5 [constant V(2,2)] vector passes) vs time; launch-latency-bound coarse levels count against it
     if last_iters > 0 and cg_ms > 0:
         ncl = ncell // world
-        vec_passes = (10 + (11.5 if args.precond == "mg" else 0)) * last_iters + 16
+        vec_passes = (10 + {"mg": 5.25, "mg_const": 11.5, "none": 0}[args.precond]) * last_iters + 16
         roof_p = {"what": "pressure phase (PCG: k_cg_* + k_mg_*)", "cg_iters": last_iters, "ms": cg_ms,
                   "alg_bytes": vec_passes * rbytes * ncl, "achieved": vec_passes * rbytes * ncl / cg_ms / 1e6,
                   "frac": vec_passes * rbytes * ncl / cg_ms / 1e6 / peak}

@@ -27,7 +27,9 @@ typedef struct ink_ctx ink_ctx;
 
 enum { INK_ARITH_STRICT = 0, INK_ARITH_FAST = 1 };
 enum { INK_FIELD_OLD = 0, INK_FIELD_CURR = 1, INK_FIELD_CURL = 2 };
-enum { INK_PCG_NONE = 0, INK_PCG_MG = 1 };
+/* INK_PCG_MG: V(2,2), piecewise-constant transfer (csrc/mg.cuh); INK_PCG_MG_TRI (default): V(1,1), trilinear transfer
+ * (csrc/mg_tri.cuh) — fewer CG iterations and less than half the passes per iteration */
+enum { INK_PCG_NONE = 0, INK_PCG_MG = 1, INK_PCG_MG_TRI = 2 };
 
 /* Run-time copy of the reference's compile-time globals (src/system.h:13-38) + solver knobs. */
 typedef struct ink_params {
@@ -51,7 +53,7 @@ typedef struct ink_params {
     int32_t cg_max_iters;
     int32_t cg_check_every; /* iterations between host convergence polls */
     int32_t cg_warm_start;  /* 1: start from the previous step's pressure */
-    int32_t cg_precond;     /* INK_PCG_NONE | INK_PCG_MG */
+    int32_t cg_precond;     /* INK_PCG_NONE | INK_PCG_MG | INK_PCG_MG_TRI */
     int32_t resort_interval;/* re-bin particles by cell every this many particle updates (0 = never) */
     /* multi-GPU (one process per GPU).  world_size==1: single device. */
     int32_t rank, world_size;

@@ -10,7 +10,7 @@ LIB_PATH = os.path.join(_HERE, "libinkb200.so")
 
 ARITH_STRICT, ARITH_FAST = 0, 1
 FIELD_OLD, FIELD_CURR, FIELD_CURL = 0, 1, 2
-PCG_NONE, PCG_MG = 0, 1
+PCG_NONE, PCG_MG, PCG_MG_TRI = 0, 1, 2
 
 
 class InkParams(C.Structure):

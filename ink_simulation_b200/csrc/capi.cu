@@ -17,6 +17,7 @@
 #include "grid_kernels.cuh"
 #include "mg.cuh"
 #include "mg_vec.cuh"
+#include "mg_tri.cuh"
 #include "nccl_shim.h"
 #include "particle_kernels.cuh"
 
@@ -111,6 +112,7 @@ struct Ctx final : CtxBase {
     MgTailArgs mg_tail{};
     size_t mg_tail_smem = 0;
     bool use_mg = false;
+    bool mg_tri = false;   // trilinear V(1,1) (mg_tri.cuh) instead of piecewise-constant V(2,2) (mg.cuh)
     int prev_iters = 0;
     // multi-GPU: overlapping-Schwarz extension of the slab the V-cycle runs on (mg_vec.cuh)
     int ovl = 0, je0 = 0, je1 = 0;        // overlap rows; extended slab [je0, je1)
@@ -227,8 +229,10 @@ struct Ctx final : CtxBase {
             scan_n.push_back(m);
         }
         for (auto& e : ev) CK(cudaEventCreate(&e));
-        if (P.cg_precond == INK_PCG_MG)
+        if (P.cg_precond == INK_PCG_MG || P.cg_precond == INK_PCG_MG_TRI) {
+            mg_tri = (P.cg_precond == INK_PCG_MG_TRI);
             if (int rc = mg_setup()) return rc;
+        }
         maxv_valid = true;  // zero field: max speed bits already 0
         seed_valid = true;
         CK(cudaStreamSynchronize(stream));
@@ -726,7 +730,7 @@ struct Ctx final : CtxBase {
             while (true) {
                 T.d[T.nlev++] = d;
                 total += 3ll * d.X * d.Y * d.Z;
-                if ((long long)d.X * d.Y * d.Z <= 16 || T.nlev == kMgMaxLevels) break;
+                if ((long long)d.X * d.Y * d.Z <= (mg_tri ? kMg3CoarsestCells : 16) || T.nlev == kMgMaxLevels) break;
                 d = MgDims{(d.X + 1) / 2, (d.Y + 1) / 2, (d.Z + 1) / 2, 0, (d.Y + 1) / 2};
             }
             return (size_t)total * sizeof(Real);
@@ -759,6 +763,7 @@ struct Ctx final : CtxBase {
             }
         }
         CK(cudaFuncSetAttribute(k_mg_tail<Real>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mg_tail_smem));
+        CK(cudaFuncSetAttribute(k_mg3_tail<Real>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mg_tail_smem));
         use_mg = true;
         return 0;
     }
@@ -769,6 +774,30 @@ struct Ctx final : CtxBase {
     // z = B r : one V-cycle; the result is lv[0].xa; the last kernel also sets S->rz_old, S->rz = <r, z>
     int mg_vcycle(const Real* r0) {
         auto rhs = [&](int l) -> const Real* { return l == 0 ? r0 : lv[l].r; };
+        if (mg_tri) {
+            // V(1,1), trilinear transfer: 3 launches per global level (residual, restrict | up), xb = residual scratch
+            for (int l = 0; l < mg_lt; ++l) {
+                const MgDims &df = lv[l].d, &dc = lv[l + 1].d;
+                if (df.Z % 4 == 0) {
+                    const long long nv = (long long)df.X * (df.j1 - df.j0) * (df.Z / 4);
+                    LAUNCH((k_mg3_residual_v4<Real>), (unsigned int)std::min<long long>(kMgBlocks, std::max<long long>(1, (nv + 255) / 256)), 256, S, df, rhs(l), lv[l].xb);
+                } else LAUNCH((k_mg3_residual<Real>), mg_blocks(df), 256, S, df, rhs(l), lv[l].xb);
+                LAUNCH((k_mg3_restrict<Real>), mg_blocks(dc), 256, S, df, dc, lv[l].xb, lv[l + 1].r);
+            }
+            {
+                const MgDims& d = lv[mg_lt].d;
+                const long long off = (long long)d.j0 * d.X * d.Z;
+                k_mg3_tail<Real><<<1, kMgTailThreads, mg_tail_smem, stream>>>(S, mg_tail, rhs(mg_lt) + off, lv[mg_lt].xa + off);
+                ++stats.kernel_launches;
+            }
+            for (int l = mg_lt - 1; l >= 0; --l) {
+                const MgDims &df = lv[l].d, &dc = lv[l + 1].d;
+                if (l == 0) LAUNCH((k_mg3_up<Real, true>), mg_blocks(dc), 256, S, df, dc, lv[l].s, rhs(l), lv[l + 1].xa, lv[l].xa, dot0, dot1);
+                else LAUNCH((k_mg3_up<Real, false>), mg_blocks(dc), 256, S, df, dc, lv[l].s, rhs(l), lv[l + 1].xa, lv[l].xa, 0, 0);
+            }
+            CK(cudaGetLastError());
+            return 0;
+        }
         auto vblocks = [](const MgDims& d, int per) {   // one thread per `per` cells
             const long long n = (long long)d.X * (d.j1 - d.j0) * (d.Z / per);
             return (unsigned int)std::min<long long>(kMgBlocks, std::max<long long>(1, (n + 255) / 256));
@@ -1057,7 +1086,7 @@ void ink_default_params(ink_params* p) {
     p->gravity[0] = 0.f; p->gravity[1] = -0.1f; p->gravity[2] = 0.f;
     p->k_cfl = 0.2f; p->dt_min = 0.005f; p->dt_max = 1.f; p->buffer_size = 3;
     p->precision = 32; p->arith = INK_ARITH_STRICT; p->device = 0;
-    p->cg_rtol = 1e-6; p->cg_max_iters = 20000; p->cg_check_every = 16; p->cg_warm_start = 1; p->cg_precond = INK_PCG_MG;
+    p->cg_rtol = 1e-6; p->cg_max_iters = 20000; p->cg_check_every = 16; p->cg_warm_start = 1; p->cg_precond = INK_PCG_MG_TRI;
     p->resort_interval = 16;
     p->rank = 0; p->world_size = 1;
 }

@@ -108,7 +108,7 @@ class System:
         if cg_warm_start is not None:
             p.cg_warm_start = int(cg_warm_start)
         if cg_precond is not None:
-            p.cg_precond = {"none": _capi.PCG_NONE, "mg": _capi.PCG_MG}[cg_precond]
+            p.cg_precond = {"none": _capi.PCG_NONE, "mg_const": _capi.PCG_MG, "mg": _capi.PCG_MG_TRI}[cg_precond]
         if resort_interval is not None:
             p.resort_interval = resort_interval
         # multi-GPU: one process per GPU; the grid is split in y-slabs, particles by index (include/ink_capi.h)
