@@ -8,6 +8,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -112,6 +113,8 @@ struct Ctx final : CtxBase {
     MgTailArgs mg_tail{};
     size_t mg_tail_smem = 0;
     bool use_mg = false;
+    bool mg_fuse = true;    // INK_MG3_UNFUSED=1 (debug / A-B): separate residual and full 4x4x4 restriction kernels
+    size_t mg_tail_cap = 200 * 1024;   // INK_MG_TAIL_KB: shared-memory budget of the single-block tail (experiments)
     bool mg_tri = false;   // trilinear V(1,1) (mg_tri.cuh) instead of piecewise-constant V(2,2) (mg.cuh)
     int prev_iters = 0;
     // multi-GPU: overlapping-Schwarz extension of the slab the V-cycle runs on (mg_vec.cuh)
@@ -698,7 +701,12 @@ struct Ctx final : CtxBase {
 
     // ---- multigrid hierarchy ------------------------------------------------------------------------
     int mg_setup() {
-        const size_t smem_cap = 200 * 1024;
+        if (const char* e = getenv("INK_MG3_UNFUSED")) mg_fuse = (atoi(e) == 0);
+        if (const char* e = getenv("INK_MG_TAIL_KB")) mg_tail_cap = (size_t)std::max(1, atoi(e)) * 1024;
+        // measured (B200, 128x256x128): a tail holding only the coarsest (<= 1024-cell) level beats a deeper single-block tail
+        // (2.59 vs 2.73 ms/step): one block of 1024 threads is issue-bound on the 8192-cell level
+        if (mg_tri && !getenv("INK_MG_TAIL_KB")) mg_tail_cap = 16 * 1024;
+        const size_t smem_cap = std::min<size_t>(mg_tail_cap, 200 * 1024);
         std::vector<MgDims> abs_d;
         je0 = g.j0; je1 = g.j1; dot0 = g.j0; dot1 = g.j1;
         if (world > 1) {
@@ -778,6 +786,12 @@ struct Ctx final : CtxBase {
             // V(1,1), trilinear transfer: 3 launches per global level (residual, restrict | up), xb = residual scratch
             for (int l = 0; l < mg_lt; ++l) {
                 const MgDims &df = lv[l].d, &dc = lv[l + 1].d;
+                if (df.Z % 4 == 0 && mg_fuse) {   // residual + z-restriction fused (xb holds the half-size z-restricted residual)
+                    const long long nv = (long long)df.X * (df.j1 - df.j0) * (df.Z / 4);
+                    LAUNCH((k_mg3_residual_rz_v4<Real>), (unsigned int)std::min<long long>(kMgBlocks, std::max<long long>(1, (nv + 255) / 256)), 256, S, df, rhs(l), lv[l].xb);
+                    LAUNCH((k_mg3_restrict_xy<Real>), mg_blocks(dc), 256, S, df, dc, lv[l].xb, lv[l + 1].r);
+                    continue;
+                }
                 if (df.Z % 4 == 0) {
                     const long long nv = (long long)df.X * (df.j1 - df.j0) * (df.Z / 4);
                     LAUNCH((k_mg3_residual_v4<Real>), (unsigned int)std::min<long long>(kMgBlocks, std::max<long long>(1, (nv + 255) / 256)), 256, S, df, rhs(l), lv[l].xb);

@@ -32,9 +32,9 @@ template <class Real, int V>
 struct alignas(sizeof(Real) * V) Pack { Real a[V]; };
 
 template <class Real, int V>
-__device__ __forceinline__ Pack<Real, V> ldp(const Real* p) { return *reinterpret_cast<const Pack<Real, V>*>(p); }
+INK_HD Pack<Real, V> ldp(const Real* p) { return *reinterpret_cast<const Pack<Real, V>*>(p); }
 template <class Real, int V>
-__device__ __forceinline__ void stp(Real* p, const Pack<Real, V>& v) { *reinterpret_cast<Pack<Real, V>*>(p) = v; }
+INK_HD void stp(Real* p, const Pack<Real, V>& v) { *reinterpret_cast<Pack<Real, V>*>(p) = v; }
 
 // block-level fp64 sum -> S->partial[slot][block]; the last block to arrive adds all partials in a fixed order
 // and returns true (thread 0 of that block holds the total in `total`).

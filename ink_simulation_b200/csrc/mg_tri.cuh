@@ -79,6 +79,94 @@ INK_HD void mg3_interp4(Real v0, Real v1, Real v2, Real (&o)[4]) {
     o[3] = Real(0.75) * v2 + Real(0.25) * v1;
 }
 
+INK_HD float hd_fma(float a, float b, float c) { return fmaf(a, b, c); }
+INK_HD double hd_fma(double a, double b, double c) { return fma(a, b, c); }
+// same, unscaled (x4): 3 * main donor + second donor, one FMA each
+template <class Real>
+INK_HD void mg3_interp4u(Real v0, Real v1, Real v2, Real (&o)[4]) {
+    o[0] = hd_fma(Real(3), v0, v1);
+    o[1] = hd_fma(Real(3), v1, v0);
+    o[2] = hd_fma(Real(3), v1, v2);
+    o[3] = hd_fma(Real(3), v2, v1);
+}
+
+// mg3_up for ONE coarse cell whose 3x3 coarse columns and 4x4 fine columns all exist (x, y interior; warp-uniform when a
+// warp walks z) on a level with even Z and 2*sizeof(Real)-aligned arrays: no x/y predicates, the z ends are handled by
+// two flags, the fine pairs (2K, 2K+1) move as one 64/128-bit access, interpolation is 1 FMA per value (x64 scaling
+// folded into the x' FMA).  Same operator as the generic path (different rounding order).
+template <class Real>
+INK_HD double mg3_up_cell_fast(const MgDims& df, const MgDims& dc, Real cj, const Real* __restrict__ r, const Real* __restrict__ e, Real* __restrict__ z,
+                               int I, int J, int K, int dj0, int dj1) {
+    const Real a0 = Real(1) - Real(kMgOmega), a1 = Real(kMgOmega) / Real(6), sc = Real(1) / Real(64);
+    const bool zlo = K > 0, zhi = K + 1 < dc.Z;
+    const long long sxc = dc.Z, syc = (long long)dc.X * dc.Z, sxf = df.Z, syf = (long long)df.X * df.Z;
+    const Real* __restrict__ eb = e + mg_idx(dc, I - 1, J - 1, K);
+    Real tz[3][3][4];
+#pragma unroll
+    for (int a = 0; a < 3; ++a)
+#pragma unroll
+        for (int b = 0; b < 3; ++b) {
+            const Real* __restrict__ p = eb + a * sxc + b * syc;
+            const Real e1 = p[0], e0 = zlo ? p[-1] : Real(0), e2 = zhi ? p[1] : Real(0);
+            mg3_interp4u(e0, e1, e2, tz[a][b]);
+        }
+    Real ty[3][4][4];
+#pragma unroll
+    for (int a = 0; a < 3; ++a)
+#pragma unroll
+        for (int m = 0; m < 4; ++m) {
+            Real o[4];
+            mg3_interp4u(tz[a][0][m], tz[a][1][m], tz[a][2][m], o);
+#pragma unroll
+            for (int n = 0; n < 4; ++n) ty[a][n][m] = o[n];
+        }
+    Real xp[4][4][4], rin[2][2][2];
+    const long long fb = mg_idx(df, 2 * I - 1, 2 * J - 1, 2 * K);
+#pragma unroll
+    for (int n = 0; n < 4; ++n)
+#pragma unroll
+        for (int l = 0; l < 4; ++l) {
+            const bool lo = (l == 0 || l == 3), no = (n == 0 || n == 3);
+            if (lo && no) continue;
+            const Real* __restrict__ p = r + fb + l * sxf + n * syf;
+            const Pack<Real, 2> q = ldp<Real, 2>(p);
+            Real pe[4];
+#pragma unroll
+            for (int m = 0; m < 4; ++m) {
+                Real o[4];
+                mg3_interp4u(ty[0][n][m], ty[1][n][m], ty[2][n][m], o);
+                pe[m] = o[l];
+            }
+            xp[l][n][1] = hd_fma(sc, pe[1], cj * q.a[0]);
+            xp[l][n][2] = hd_fma(sc, pe[2], cj * q.a[1]);
+            if (!lo && !no) {
+                rin[l - 1][n - 1][0] = q.a[0]; rin[l - 1][n - 1][1] = q.a[1];
+                xp[l][n][0] = zlo ? hd_fma(sc, pe[0], cj * p[-1]) : Real(0);
+                xp[l][n][3] = zhi ? hd_fma(sc, pe[3], cj * p[2]) : Real(0);
+            }
+        }
+    double acc = 0;
+#pragma unroll
+    for (int n = 1; n < 3; ++n) {
+        const int fj = 2 * J - 1 + n;
+        const bool in_dot = (fj >= dj0) && (fj < dj1);
+#pragma unroll
+        for (int l = 1; l < 3; ++l) {
+            Pack<Real, 2> o;
+#pragma unroll
+            for (int m = 1; m < 3; ++m) {
+                const Real nb = (xp[l - 1][n][m] + xp[l + 1][n][m]) + (xp[l][n - 1][m] + xp[l][n + 1][m]) + (xp[l][n][m - 1] + xp[l][n][m + 1]);
+                const Real rr = rin[l - 1][n - 1][m - 1];
+                const Real v = hd_fma(a1, nb, hd_fma(a0, xp[l][n][m], cj * rr));
+                o.a[m - 1] = v;
+                if (in_dot) acc += (double)rr * (double)v;
+            }
+            stp<Real, 2>(z + fb + l * sxf + n * syf, o);
+        }
+    }
+    return acc;
+}
+
 // z = c r + (1-omega) x' + (omega/6) N x',  x' = c r + P e.  One thread per COARSE cell (I,J,K) = the 2x2x2 fine block
 // (2I+a, 2J+b, 2K+q): the 27 coarse values around it give P e on the 4x4x4 fine cells 2I-1..2I+2 (separable
 // interpolation in registers); x' is formed there (0 outside the grid / slab, which is exactly "N sums in-grid neighbours
@@ -89,8 +177,13 @@ INK_HD double mg3_up(const MgDims& df, const MgDims& dc, Real s, const Real* __r
                      long long tid, long long nth, int dj0 = 0, int dj1 = 0x7fffffff) {
     const Real cj = Real(kMgOmega) / (Real(6) * s), a0 = Real(1) - Real(kMgOmega), a1 = Real(kMgOmega) / Real(6);
     double acc = 0;
+    const bool vec_ok = ((df.Z & 1) == 0) && ((((unsigned long long)r | (unsigned long long)z) & (2 * sizeof(Real) - 1)) == 0);
     INK_MG_CELL_LOOP(dc, tid, nth) {
         const int I = it_.i, K = it_.k, J = dc.j0 + it_.jl;
+        if (vec_ok && I >= 1 && I + 1 < dc.X && 2 * I + 2 < df.X && J - 1 >= dc.j0 && J + 1 < dc.j1 && 2 * J - 1 >= df.j0 && 2 * J + 2 < df.j1) {
+            acc += mg3_up_cell_fast<Real>(df, dc, cj, r, e, z, I, J, K, dj0, dj1);
+            continue;
+        }
         // P e on the 4x4x4 block: z, then y, then x
         Real tz[3][3][4];
 #pragma unroll
@@ -218,6 +311,75 @@ __global__ void __launch_bounds__(256) k_mg3_up(CgScal* S, MgDims df, MgDims dc,
         if (block_sum_last(acc, S, 0, tot)) {
             if (threadIdx.x == 0) { if (S->dist) S->loc[2] = tot; else { S->rz_old = S->rz; S->rz = tot; } }
         }
+    }
+}
+
+// ---- fused down-pass for levels with Z % 4 == 0 --------------------------------------------------------------------
+// k_mg3_residual_rz_v4: res = r - (omega/6) M r for 4 z-consecutive cells per thread, restricted along z on the fly:
+//   resz[i, j, K] = 1/4 res[2K-1] + 3/4 res[2K] + 3/4 res[2K+1] + 1/4 res[2K+2]      (layout (Y, X, Z/2), z fastest)
+// The two values a thread lacks (res[k-1], res[k+4]) come from the neighbouring lanes by warp shuffle; a lane at a warp
+// edge whose neighbour cell is in another warp recomputes that one residual itself.  The full-size residual is never
+// written: 2 B/cell out instead of 4, and the x-y part (k_mg3_restrict_xy) reads 2 B/cell, unit stride along z.
+template <class Real>
+__device__ __forceinline__ Real mg3_res_at(const MgDims& d, const Real* __restrict__ r, int i, int j, int k) {
+    const long long c = mg_idx(d, i, j, k);
+    const Real rc = r[c];
+    return rc - (Real(kMgOmega) / Real(6)) * (Real(6) * rc - mg_nbr_sum(d, r, i, j, k, c));
+}
+template <class Real>
+__global__ void __launch_bounds__(256) k_mg3_residual_rz_v4(const CgScal* S, MgDims d, const Real* __restrict__ r, Real* __restrict__ resz) {
+    if (S->done) return;
+    const Real w6 = Real(kMgOmega) / Real(6);
+    const unsigned int ZV = (unsigned int)d.Z >> 2;
+    const unsigned int tot = (unsigned int)(d.j1 - d.j0) * (unsigned int)d.X * ZV;
+    const unsigned int lane = threadIdx.x & 31u;
+    for (unsigned int base = blockIdx.x * blockDim.x + threadIdx.x - lane; base < tot; base += gridDim.x * blockDim.x) {   // warp-uniform trip count
+        int i = 0, j = 0, k = 0; long long c = 0;
+        Real res[4] = {Real(0), Real(0), Real(0), Real(0)};
+        const bool act = mg_vec_cell(d, base + lane, i, j, k, c);
+        if (act) {
+            const P4<Real> rc = ldp<Real, 4>(r + c);
+            Real L[4];
+            mg_lap4<Real>(d, r, rc, i, j, k, c, L);
+#pragma unroll
+            for (int a = 0; a < 4; ++a) res[a] = rc.a[a] - w6 * L[a];
+        }
+        Real left = __shfl_up_sync(0xffffffffu, res[3], 1);
+        Real right = __shfl_down_sync(0xffffffffu, res[0], 1);
+        if (act) {
+            if (k == 0) left = Real(0);
+            else if (lane == 0) left = mg3_res_at<Real>(d, r, i, j, k - 1);
+            if (k + 4 >= d.Z) right = Real(0);
+            else if (lane == 31) right = mg3_res_at<Real>(d, r, i, j, k + 4);
+            Pack<Real, 2> o;
+            o.a[0] = Real(0.25) * (left + res[2]) + Real(0.75) * (res[0] + res[1]);
+            o.a[1] = Real(0.25) * (res[1] + right) + Real(0.75) * (res[2] + res[3]);
+            stp<Real, 2>(resz + (c >> 1), o);   // c = row * Z + k, Z and k even: (row * Z/2 + k/2)
+        }
+    }
+}
+// rc[I,J,K] = sum over the 4x4 fine columns (2I-1..2I+2, 2J-1..2J+2) of wx wy resz[.,.,K]
+template <class Real>
+__global__ void __launch_bounds__(256) k_mg3_restrict_xy(const CgScal* S, MgDims df, MgDims dc, const Real* __restrict__ resz, Real* __restrict__ rc) {
+    if (S->done) return;
+    INK_MG_CELL_LOOP(dc, (long long)blockIdx.x * blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x) {
+        INK_MG_DECODE(dc)
+        Real acc = Real(0);
+#pragma unroll
+        for (int n = 0; n < 4; ++n) {
+            const int fj = 2 * j - 1 + n;
+            if (fj < df.j0 || fj >= df.j1) continue;
+            const Real wy = (n == 1 || n == 2) ? Real(0.75) : Real(0.25);
+            Real a = Real(0);
+#pragma unroll
+            for (int l = 0; l < 4; ++l) {
+                const int fi = 2 * i - 1 + l;
+                if (fi < 0 || fi >= df.X) continue;
+                a += ((l == 1 || l == 2) ? Real(0.75) : Real(0.25)) * resz[((long long)fj * df.X + fi) * dc.Z + k];
+            }
+            acc += wy * a;
+        }
+        rc[c] = acc;
     }
 }
 
