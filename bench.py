@@ -191,6 +191,7 @@ def main():
     ap.add_argument("--cpu-steps", type=int, default=1, help="oracle steps for cpu_baseline (0 = skip)")
     ap.add_argument("--cpu-particles", type=int, default=10_000_000)
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-blocking", action="store_true", help="e2e through the blocking set/solve/get calls instead of the streaming ones")
     ap.add_argument("--no-kernels", action="store_true", help="skip the per-kernel roofline micro-timings")
     args = ap.parse_args()
 
@@ -272,19 +273,44 @@ def main():
     # ---- e2e: host positions in -> solve -> host positions out, every step ------------------------------
     e2e = None
     if not args.no_e2e:
+        # Every step: positions come from pinned host memory (H2D, 12 B/particle), System::solve runs, the new positions go
+        # back to pinned host memory (D2H, 12 B/particle).  Streaming calls of the C ABI (ink_prefetch_positions /
+        # ink_commit_positions / ink_step / ink_fetch_positions_async): the copies run on their own streams, so the upload of
+        # step i+1's input and the download of step i's result overlap the compute in between (inputs are independent host
+        # buffers, as with a producer feeding frames; results land one step later).  All copies of the k2 steps start and
+        # finish inside the timed region (sync_io before the closing event).  --e2e-blocking: the serial set/solve/get calls.
         S.get_particles(0, out_pos=out_host)
-        k2 = max(3, args.steps // 4)
-        barrier()
-        e0.record()
-        for _ in range(k2):
-            S.set_particles_shard(out_host)       # H2D from pinned memory (+ re-binning); every rank its own shard
-            S.solve(RENDER_DT)
-            S.get_particles(0, out_pos=out_host)  # D2H into pinned memory, caller's particle order
-        e1.record()
+        in_bufs = [out_host.clone().pin_memory(), out_host.clone().pin_memory()]   # two producer buffers holding the current cloud
+        out_bufs = [out_host, torch.empty_like(out_host).pin_memory()]
+        k2 = max(3, args.steps)
+        if args.e2e_blocking:
+            barrier()
+            e0.record()
+            for i in range(k2):
+                S.set_particles_shard(in_bufs[i & 1])
+                S.solve(RENDER_DT)
+                S.get_particles(0, out_pos=out_bufs[i & 1])
+            e1.record()
+        else:
+            for i in range(2):   # warm the staging buffers / streams (untimed)
+                S.prefetch_positions(in_bufs[i & 1]); S.commit_positions(); S.solve(RENDER_DT); S.fetch_positions_async(out_bufs[i & 1])
+            S.sync_io()
+            barrier()
+            e0.record()
+            S.prefetch_positions(in_bufs[0])
+            for i in range(k2):
+                S.commit_positions()
+                if i + 1 < k2:
+                    S.prefetch_positions(in_bufs[(i + 1) & 1])
+                S.solve(RENDER_DT)
+                S.fetch_positions_async(out_bufs[i & 1])
+            S.sync_io()
+            e1.record()
         barrier()
         ms_e2e = max_over_ranks(e0.elapsed_time(e1)) / k2
         e2e = {"value": n / (ms_e2e * 1e-3), "unit": "particle-updates/s", "ms_per_step": ms_e2e,
-               "h2d_bytes_per_step": n * 12, "d2h_bytes_per_step": n * 12}
+               "h2d_bytes_per_step": n_local * 12, "d2h_bytes_per_step": n_local * 12,
+               "mode": "blocking calls" if args.e2e_blocking else "streaming calls: H2D(i+1) and D2H(i-1) overlap step i", "steps": k2}
 
     # ---- per-kernel roofline micro-timings (CUDA events, same process, after the timed region) -------------
     peak, peak_src = peaks()

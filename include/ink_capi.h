@@ -115,6 +115,18 @@ int  ink_velocity_field_update(ink_ctx* c, double dt);  /* updateVelocityField:4
 int  ink_particles(ink_ctx* c, double dt);              /* updateParticles    src/inkSolver.cpp:44-84 */
 int  ink_resort_particles(ink_ctx* c);                  /* re-bin now (no reference equivalent; layout only) */
 
+/* ---- streaming particle I/O (no reference equivalent: the reference keeps m_ink in host memory) ------------------
+ * For callers that feed positions from the host every step and read them back every step (the per-frame .ply writer of
+ * src/inkSim.cpp:45-96, bench.py's e2e leg).  Copies run on two dedicated copy streams with double-buffered device
+ * staging, so the H2D of the next input and the D2H of the last result overlap the ink_step in between:
+ *     ink_prefetch_positions(next)  ->  ink_commit_positions  ->  ink_step  ->  ink_fetch_positions_async(out)
+ * Buffers should be pinned host memory (pageable memory works but serialises).  ink_commit_positions replaces the
+ * positions of an existing drop (same count; binning and order kept), i.e. ink_set_particles without re-binning. */
+int  ink_prefetch_positions(ink_ctx* c, int drop, const void* pos_xyz, int64_t n, int host_dtype);
+int  ink_commit_positions(ink_ctx* c, int drop);
+int  ink_fetch_positions_async(ink_ctx* c, int drop, void* pos_xyz, int host_dtype);
+int  ink_sync_io(ink_ctx* c);   /* all outstanding copies and the compute stream are done */
+
 int  ink_get_stats(ink_ctx* c, ink_stats* out);
 /* Device-time of every phase of the last ink_step in ms: dt, advect, forces, viscosity, pressure, vorticity, particles, resort */
 int  ink_get_phase_ms(ink_ctx* c, float out[8]);

@@ -68,6 +68,10 @@ SYMBOLS = {
     "ink_velocity_field_update": (_I, [_VP, _D]),
     "ink_particles": (_I, [_VP, _D]),
     "ink_resort_particles": (_I, [_VP]),
+    "ink_prefetch_positions": (_I, [_VP, _I, _VP, _L, _I]),
+    "ink_commit_positions": (_I, [_VP, _I]),
+    "ink_fetch_positions_async": (_I, [_VP, _I, _VP, _I]),
+    "ink_sync_io": (_I, [_VP]),
     "ink_get_stats": (_I, [_VP, C.POINTER(InkStats)]),
     "ink_get_phase_ms": (_I, [_VP, C.POINTER(C.c_float)]),
 }

@@ -88,6 +88,10 @@ struct CtxBase {
     virtual int velocity_field_update(double dt) = 0;
     virtual int particles(double dt) = 0;
     virtual int resort() = 0;
+    virtual int prefetch_positions(int drop, const void* pos, int64_t n, int hd) = 0;
+    virtual int commit_positions(int drop) = 0;
+    virtual int fetch_positions_async(int drop, void* pos, int hd) = 0;
+    virtual int sync_io() = 0;
     virtual int phase_ms(float out[8]) = 0;
 };
 
@@ -146,6 +150,15 @@ struct Ctx final : CtxBase {
     size_t stage_bytes = 0;
     cudaEvent_t ev[10]{};
     bool ev_valid = false;
+    // streaming particle I/O (ink_prefetch_positions / ink_commit_positions / ink_fetch_positions_async): two copy streams
+    // beside the compute stream, double-buffered device staging, so H2D of the next input and D2H of the last result
+    // overlap the step in between
+    cudaStream_t s_in = nullptr, s_out = nullptr;
+    void* io_in[2] = {nullptr, nullptr};
+    void* io_out[2] = {nullptr, nullptr};
+    size_t io_in_bytes = 0, io_out_bytes = 0;
+    cudaEvent_t ev_in_ready[2]{}, ev_in_free[2]{}, ev_out_ready[2]{}, ev_out_done[2]{};
+    int in_next = 0, out_next = 0, in_pending = -1, in_pending_drop = -1, in_pending_hd = 32;
 
     ~Ctx() override {
         if (comm) nccl().CommDestroy(comm);
@@ -164,6 +177,13 @@ struct Ctx final : CtxBase {
         cudaFree(stage);
         for (auto& e : ev)
             if (e) cudaEventDestroy(e);
+        for (int b = 0; b < 2; ++b) {
+            cudaFree(io_in[b]); cudaFree(io_out[b]);
+            for (cudaEvent_t e : {ev_in_ready[b], ev_in_free[b], ev_out_ready[b], ev_out_done[b]})
+                if (e) cudaEventDestroy(e);
+        }
+        if (s_in) cudaStreamDestroy(s_in);
+        if (s_out) cudaStreamDestroy(s_out);
     }
     void free_particles() {
         for (auto& pp : part) {
@@ -468,6 +488,89 @@ struct Ctx final : CtxBase {
         if (pos && !dpos) CK(cudaMemcpyAsync(pos, op, bytes, cudaMemcpyDeviceToHost, stream));
         if (vel_ && !dvel) CK(cudaMemcpyAsync(vel_, ov, bytes, cudaMemcpyDeviceToHost, stream));
         CK(cudaStreamSynchronize(stream));
+        return 0;
+    }
+
+    // ---- streaming particle I/O ----------------------------------------------------------------------------------
+    int io_setup() {
+        if (s_in) return 0;
+        CK(cudaStreamCreateWithFlags(&s_in, cudaStreamNonBlocking));
+        CK(cudaStreamCreateWithFlags(&s_out, cudaStreamNonBlocking));
+        for (int b = 0; b < 2; ++b) {
+            CK(cudaEventCreateWithFlags(&ev_in_ready[b], cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&ev_in_free[b], cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&ev_out_ready[b], cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&ev_out_done[b], cudaEventDisableTiming));
+        }
+        return 0;
+    }
+    // start the H2D copy of the next positions of `drop` (same particle count as now; pinned host memory makes it truly
+    // asynchronous) on the input copy stream; returns at once
+    int prefetch_positions(int drop, const void* pos, int64_t n, int hd) override {
+        if (int rc = check_hd(hd, err)) return rc;
+        if (drop < 0 || drop >= (int)drop_n.size() || n != drop_n[drop]) { err = "prefetch_positions: drop must exist with the same particle count (use ink_set_particles first)"; return 2; }
+        if (in_pending >= 0) { err = "prefetch_positions: a prefetched buffer is waiting for ink_commit_positions"; return 2; }
+        if (int rc = io_setup()) return rc;
+        const size_t bytes = (size_t)n * 3 * (hd == 64 ? 8 : 4);
+        if (bytes > io_in_bytes) {
+            CK(cudaDeviceSynchronize());
+            for (int b = 0; b < 2; ++b) { cudaFree(io_in[b]); io_in[b] = nullptr; CK(cudaMalloc(&io_in[b], bytes)); }
+            io_in_bytes = bytes;
+        }
+        const int b = in_next;
+        CK(cudaStreamWaitEvent(s_in, ev_in_free[b], 0));     // the import kernel that last read this buffer
+        if (is_device_ptr(pos)) CK(cudaMemcpyAsync(io_in[b], pos, bytes, cudaMemcpyDeviceToDevice, s_in));
+        else CK(cudaMemcpyAsync(io_in[b], pos, bytes, cudaMemcpyHostToDevice, s_in));
+        CK(cudaEventRecord(ev_in_ready[b], s_in));
+        in_pending = b; in_pending_drop = drop; in_pending_hd = hd;
+        in_next ^= 1;
+        return 0;
+    }
+    // make the prefetched positions the state of the drop: the compute stream waits for the copy, then gathers them into the
+    // binned slots (binning and velocities kept; the periodic re-binning of ink_step keeps the layout tight)
+    int commit_positions(int drop) override {
+        if (in_pending < 0 || in_pending_drop != drop) { err = "commit_positions: nothing prefetched for this drop"; return 2; }
+        const int b = in_pending;
+        CK(cudaStreamWaitEvent(stream, ev_in_ready[b], 0));
+        if (in_pending_hd == 64) LAUNCH((k_import_pos_perm<double, Real>), nblk(np), 256, np, drop_off[drop], drop_n[drop], part[pcur], (const double*)io_in[b]);
+        else LAUNCH((k_import_pos_perm<float, Real>), nblk(np), 256, np, drop_off[drop], drop_n[drop], part[pcur], (const float*)io_in[b]);
+        CK(cudaGetLastError());
+        CK(cudaEventRecord(ev_in_free[b], stream));
+        in_pending = -1;
+        seed_valid = false;
+        return 0;
+    }
+    // positions of `drop` (caller order) -> pos, asynchronously: export on the compute stream, D2H on the output copy
+    // stream.  `pos` is complete after ink_sync_io (or after the second next ink_fetch_positions_async returned).
+    int fetch_positions_async(int drop, void* pos, int hd) override {
+        if (int rc = check_hd(hd, err)) return rc;
+        if (drop < 0 || drop >= (int)drop_n.size()) { err = "no such drop"; return 2; }
+        const long long n = drop_n[drop];
+        if (n == 0) return 0;
+        if (int rc = io_setup()) return rc;
+        const size_t bytes = (size_t)n * 3 * (hd == 64 ? 8 : 4);
+        if (bytes > io_out_bytes) {
+            CK(cudaDeviceSynchronize());
+            for (int b = 0; b < 2; ++b) { cudaFree(io_out[b]); io_out[b] = nullptr; CK(cudaMalloc(&io_out[b], bytes)); }
+            io_out_bytes = bytes;
+        }
+        const int b = out_next;
+        CK(cudaStreamWaitEvent(stream, ev_out_done[b], 0));   // the D2H that last read this staging buffer
+        if (hd == 64) LAUNCH((k_export_aos<Real, double>), nblk(np), 256, np, drop_off[drop], n, part[pcur], (double*)io_out[b], (double*)nullptr);
+        else LAUNCH((k_export_aos<Real, float>), nblk(np), 256, np, drop_off[drop], n, part[pcur], (float*)io_out[b], (float*)nullptr);
+        CK(cudaGetLastError());
+        CK(cudaEventRecord(ev_out_ready[b], stream));
+        CK(cudaStreamWaitEvent(s_out, ev_out_ready[b], 0));
+        if (is_device_ptr(pos)) CK(cudaMemcpyAsync(pos, io_out[b], bytes, cudaMemcpyDeviceToDevice, s_out));
+        else CK(cudaMemcpyAsync(pos, io_out[b], bytes, cudaMemcpyDeviceToHost, s_out));
+        CK(cudaEventRecord(ev_out_done[b], s_out));
+        out_next ^= 1;
+        return 0;
+    }
+    int sync_io() override {
+        if (s_in) CK(cudaStreamSynchronize(s_in));
+        CK(cudaStreamSynchronize(stream));
+        if (s_out) CK(cudaStreamSynchronize(s_out));
         return 0;
     }
 
@@ -1169,6 +1272,10 @@ int ink_vorticity(ink_ctx* c, double dt) { return c->impl->vorticity(dt); }
 int ink_velocity_field_update(ink_ctx* c, double dt) { return c->impl->velocity_field_update(dt); }
 int ink_particles(ink_ctx* c, double dt) { return c->impl->particles(dt); }
 int ink_resort_particles(ink_ctx* c) { return c->impl->resort(); }
+int ink_prefetch_positions(ink_ctx* c, int drop, const void* pos, int64_t n, int hd) { return c->impl->prefetch_positions(drop, pos, n, hd); }
+int ink_commit_positions(ink_ctx* c, int drop) { return c->impl->commit_positions(drop); }
+int ink_fetch_positions_async(ink_ctx* c, int drop, void* pos, int hd) { return c->impl->fetch_positions_async(drop, pos, hd); }
+int ink_sync_io(ink_ctx* c) { return c->impl->sync_io(); }
 
 int ink_get_stats(ink_ctx* c, ink_stats* out) { *out = c->impl->stats; return 0; }
 int ink_get_phase_ms(ink_ctx* c, float out[8]) { return c->impl->phase_ms(out); }

@@ -105,6 +105,17 @@ __global__ void __launch_bounds__(256) k_import_aos(long long n, long long dst_o
     }
     P.orig[d] = (uint32_t)d;
 }
+// Streaming input (ink_commit_positions): new positions of one drop, caller order -> the binned slots the particles
+// already occupy (orig keeps the mapping).  No re-binning, velocities untouched (K8 overwrites them).
+template <class Tin, class Real>
+__global__ void __launch_bounds__(256) k_import_pos_perm(long long n, long long off, long long cnt, Particles<Real> P, const Tin* __restrict__ pos) {
+    const long long s = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    const long long o = (long long)P.orig[s] - off;
+    if (o < 0 || o >= cnt) return;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) P.p[a][s] = (Real)pos[3 * o + a];
+}
 // out[(orig - off)*3 + a] for the particles of one drop (orig in [off, off+cnt))
 template <class Real, class Tout>
 __global__ void __launch_bounds__(256) k_export_aos(long long n, long long off, long long cnt, Particles<Real> P, Tout* __restrict__ pos, Tout* __restrict__ vel) {

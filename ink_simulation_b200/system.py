@@ -293,6 +293,25 @@ class System:
     def particles(self, dt):
         self._ck(self.L.ink_particles(self.h, float(dt)))
 
+    # ---- streaming particle I/O (include/ink_capi.h): copies overlap the step in between ------------------------
+    @staticmethod
+    def _hd_of(t):
+        return (32 if t.element_size() == 4 else 64) if hasattr(t, "data_ptr") else (32 if t.dtype == np.float32 else 64)
+
+    def prefetch_positions(self, pos, drop=0):
+        """start the H2D copy of the next positions of `drop` (pinned torch tensor or numpy array, (N,3)); returns at once"""
+        self._ck(self.L.ink_prefetch_positions(self.h, drop, _ptr(pos), pos.shape[0], self._hd_of(pos)))
+
+    def commit_positions(self, drop=0):
+        self._ck(self.L.ink_commit_positions(self.h, drop))
+
+    def fetch_positions_async(self, out_pos, drop=0):
+        """export + D2H of the positions of `drop` into out_pos on the output copy stream; complete after sync_io()"""
+        self._ck(self.L.ink_fetch_positions_async(self.h, drop, _ptr(out_pos), self._hd_of(out_pos)))
+
+    def sync_io(self):
+        self._ck(self.L.ink_sync_io(self.h))
+
     def resort_particles(self):
         self._ck(self.L.ink_resort_particles(self.h))
 
