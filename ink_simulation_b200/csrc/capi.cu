@@ -11,6 +11,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "cg.cuh"
@@ -48,10 +49,22 @@ static thread_local std::string g_create_error;
         }                                                                                                \
     } while (0)
 
-#define LAUNCH(kern, grid, block, ...)                     \
-    do {                                                   \
-        kern<<<(grid), (block), 0, stream>>>(__VA_ARGS__); \
-        ++stats.kernel_launches;                           \
+// launch with the programmatic-stream-serialization attribute (see INK_PDL in common.cuh); INK_NO_PDL=1 disables it
+static const bool g_use_pdl = [] { const char* e = getenv("INK_NO_PDL"); return !(e && atoi(e) != 0); }();
+template <class... KArgs, class... Args>
+static inline void launch_k(void (*kern)(KArgs...), unsigned int grid, unsigned int block, size_t smem, cudaStream_t st, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(block); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = g_use_pdl ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, kern, KArgs(std::forward<Args>(args))...);
+}
+#define LAUNCH(kern, grid, block, ...)                                   \
+    do {                                                                 \
+        launch_k(kern, (grid), (block), 0, stream, __VA_ARGS__);         \
+        ++stats.kernel_launches;                                         \
     } while (0)
 
 static inline unsigned int nblk(long long n, int b = 256) { return (unsigned int)((n + b - 1) / b); }
@@ -904,7 +917,7 @@ struct Ctx final : CtxBase {
             {
                 const MgDims& d = lv[mg_lt].d;
                 const long long off = (long long)d.j0 * d.X * d.Z;
-                k_mg3_tail<Real><<<1, kMgTailThreads, mg_tail_smem, stream>>>(S, mg_tail, rhs(mg_lt) + off, lv[mg_lt].xa + off);
+                launch_k(k_mg3_tail<Real>, 1, kMgTailThreads, mg_tail_smem, stream, S, mg_tail, rhs(mg_lt) + off, lv[mg_lt].xa + off);
                 ++stats.kernel_launches;
             }
             for (int l = mg_lt - 1; l >= 0; --l) {
@@ -932,7 +945,7 @@ struct Ctx final : CtxBase {
         {
             const MgDims& d = lv[mg_lt].d;
             const long long off = (long long)d.j0 * d.X * d.Z;
-            k_mg_tail<Real><<<1, kMgTailThreads, mg_tail_smem, stream>>>(S, mg_tail, rhs(mg_lt) + off, lv[mg_lt].xa + off);
+            launch_k(k_mg_tail<Real>, 1, kMgTailThreads, mg_tail_smem, stream, S, mg_tail, rhs(mg_lt) + off, lv[mg_lt].xa + off);
             ++stats.kernel_launches;
         }
         for (int l = mg_lt - 1; l >= 0; --l) {
@@ -986,7 +999,7 @@ struct Ctx final : CtxBase {
     // Multi-GPU: every rank iterates on its own rows; per iteration 2 all-reduces (<d,w>; <r,r> & <r,z> together) and one
     // boundary-row exchange of z.  The preconditioner is slab-local (no traffic).
     int cg_post(int stage) {
-        k_cg_post<<<1, 32, 0, stream>>>(S, stage, use_mg ? 1 : 0);
+        launch_k(k_cg_post, 1, 32, 0, stream, S, stage, use_mg ? 1 : 0);
         ++stats.kernel_launches;
         return 0;
     }

@@ -79,6 +79,7 @@ __device__ __forceinline__ void vec_cell(const Grid& g, long long t, int ZV, int
 // r = f - M x, <r,r>, <f,f>;  (x may be a warm start)
 template <class Real, int V>
 __global__ void __launch_bounds__(256) k_cg_init(Grid g, CgScal* S, const Real* __restrict__ f, const Real* __restrict__ x, Real* __restrict__ r) {
+    INK_PDL();
     const int ZV = g.Z / V;
     const long long nvec = (long long)(g.j1 - g.j0) * g.X * ZV;
     double arr = 0, abb = 0;
@@ -150,6 +151,7 @@ __global__ void __launch_bounds__(256) k_cg_init(Grid g, CgScal* S, const Real* 
 template <class Real, int V>
 __global__ void __launch_bounds__(256) k_cg_dir_matvec(Grid g, CgScal* S, const Real* __restrict__ r, const Real* __restrict__ d,
                                                        Real* __restrict__ dn, Real* __restrict__ w, int halo_lo, int halo_hi) {
+    INK_PDL();
     if (S->done) return;
     const Real beta = (S->iters == 0) ? Real(0) : (Real)(S->rz / S->rz_old);
     const int ZV = g.Z / V;
@@ -213,6 +215,7 @@ __global__ void __launch_bounds__(256) k_cg_dir_matvec(Grid g, CgScal* S, const 
 template <class Real, int V, bool PRECOND>
 __global__ void __launch_bounds__(256) k_cg_update(Grid g, CgScal* S, Real* __restrict__ x, Real* __restrict__ r, const Real* __restrict__ d,
                                                    const Real* __restrict__ w) {
+    INK_PDL();
     if (S->done) return;
     const Real alpha = (Real)(S->rz / S->dw);
     const int ZV = g.Z / V;
@@ -251,6 +254,7 @@ __global__ void __launch_bounds__(256) k_cg_update(Grid g, CgScal* S, Real* __re
 // epilogues do.  stage 0: after k_cg_init; 1: after k_cg_dir_matvec; 2: end of iteration (rr from k_cg_update, rz from the
 // V-cycle when preconditioned, else rz = rr); 3: <r,z> of the very first V-cycle.
 __global__ void k_cg_post(CgScal* S, int stage, int precond) {
+    INK_PDL();
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     if (stage == 0) {
         S->rr = S->loc[1]; S->rr_old = S->loc[1]; S->bb = S->loc[3]; S->dw = 0;

@@ -76,4 +76,18 @@ __device__ __forceinline__ float warp_max(float v) {
 
 constexpr int kSMs = 148;  // B200
 
+// Programmatic dependent launch (sm_90+).  The step is a chain of ~300 short kernels on one stream; with plain launches
+// each pays the full launch + drain latency (2-3 us, which is most of a coarse multigrid level's kernel).  Every kernel
+// of the library therefore starts with INK_PDL(): griddepcontrol.wait blocks until the PRECEDING kernel has completed
+// and its memory is visible (a no-op for a normally launched kernel), then launch_dependents lets the NEXT kernel's
+// blocks be scheduled while this one runs (they sit in their own wait).  Nothing touches global memory before the
+// wait, so RAW and WAR hazards between consecutive kernels are ordered exactly as with plain stream serialization.
+__device__ __forceinline__ void pdl_enter() {
+#if defined(__CUDA_ARCH__) && __CUDA_ARCH__ >= 900
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+#endif
+}
+#define INK_PDL() ::ink::pdl_enter()
+
 }  // namespace ink

@@ -147,6 +147,7 @@ __device__ __forceinline__ void block_max_to_global(float m, unsigned int* out) 
 template <class Real>
 __global__ void __launch_bounds__(256) k_max_speed(Grid g, const Real* __restrict__ u, const Real* __restrict__ v,
                                                    const Real* __restrict__ w, unsigned int* out) {
+    INK_PDL();
     float m = 0.f;
     const long long cells = (long long)(g.j1 - g.j0) * g.sy;
     const long long base = (long long)g.j0 * g.sy;
@@ -167,6 +168,7 @@ __device__ __forceinline__ double trace_mid(double x, double t, double v) { retu
 template <class Real>
 __global__ void __launch_bounds__(256) k_advect(Grid g, Consts<Real> C, Real dt, const Real* __restrict__ u, const Real* __restrict__ v,
                                                 const Real* __restrict__ w, Real* __restrict__ nu, Real* __restrict__ nv, Real* __restrict__ nw) {
+    INK_PDL();
     int i, j, k; long long c;
     if (!cell_of_thread(g, (long long)blockIdx.x * blockDim.x + threadIdx.x, i, j, k, c)) return;
     const Real t = -dt;
@@ -196,6 +198,7 @@ __global__ void __launch_bounds__(256) k_advect(Grid g, Consts<Real> C, Real dt,
 template <class Real>
 __global__ void __launch_bounds__(256) k_dilate_add_gravity(Grid g, int R, const uint8_t* __restrict__ seed, uint8_t* __restrict__ mark,
                                                             Real gx, Real gy, Real gz, Real* __restrict__ u, Real* __restrict__ v, Real* __restrict__ w) {
+    INK_PDL();
     int i, j, k; long long c;
     if (!cell_of_thread(g, (long long)blockIdx.x * blockDim.x + threadIdx.x, i, j, k, c)) return;
     uint8_t m = 0;
@@ -240,6 +243,7 @@ __device__ __forceinline__ Real lap7(const Real* __restrict__ f, const Grid& g, 
 template <class Real>
 __global__ void __launch_bounds__(256) k_viscosity(Grid g, Real s, const Real* __restrict__ u, const Real* __restrict__ v, const Real* __restrict__ w,
                                                    Real* __restrict__ nu, Real* __restrict__ nv, Real* __restrict__ nw) {
+    INK_PDL();
     int i, j, k; long long c;
     if (!cell_of_thread(g, (long long)blockIdx.x * blockDim.x + threadIdx.x, i, j, k, c)) return;
     const Real lx = lap7(u, g, i, j, k, c), ly = lap7(v, g, i, j, k, c), lz = lap7(w, g, i, j, k, c);
@@ -256,6 +260,7 @@ __global__ void __launch_bounds__(256) k_viscosity(Grid g, Real s, const Real* _
 template <class Real>
 __global__ void __launch_bounds__(256) k_divergence(Grid g, int mode, Real scale, Real patm, const Real* __restrict__ u, const Real* __restrict__ v,
                                                     const Real* __restrict__ w, Real* __restrict__ out) {
+    INK_PDL();
     int i, j, k; long long c;
     if (!cell_of_thread(g, (long long)blockIdx.x * blockDim.x + threadIdx.x, i, j, k, c)) return;
     Real d = -u[c] - v[c] - w[c];
@@ -278,6 +283,7 @@ __global__ void __launch_bounds__(256) k_divergence(Grid g, int mode, Real scale
 // ------------------------------------------------------------------------------------------------
 template <class Real>
 __global__ void __launch_bounds__(256) k_grad_subtract(Grid g, Real s, const Real* __restrict__ p, Real* __restrict__ u, Real* __restrict__ v, Real* __restrict__ w) {
+    INK_PDL();
     int i, j, k; long long c;
     if (!cell_of_thread(g, (long long)blockIdx.x * blockDim.x + threadIdx.x, i, j, k, c)) return;
     const Real val = p[c];
@@ -290,15 +296,18 @@ __global__ void __launch_bounds__(256) k_grad_subtract(Grid g, Real s, const Rea
 
 template <class Tin, class Tout>
 __global__ void __launch_bounds__(256) k_convert(long long n, const Tin* __restrict__ in, Tout* __restrict__ out) {
+    INK_PDL();
     for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) out[t] = (Tout)in[t];
 }
 template <class Real>
 __global__ void __launch_bounds__(256) k_scale(long long n, Real s, Real* __restrict__ x) {
+    INK_PDL();
     for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) x[t] = s * x[t];
 }
 // q -> p = q + p_atm (and back) for the shifted Poisson unknown
 template <class Real>
 __global__ void __launch_bounds__(256) k_add_scalar(long long n, Real s, const Real* __restrict__ in, Real* __restrict__ out) {
+    INK_PDL();
     for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) out[t] = in[t] + s;
 }
 
@@ -308,6 +317,7 @@ __global__ void __launch_bounds__(256) k_add_scalar(long long n, Real s, const R
 template <class Real>
 __global__ void __launch_bounds__(256) k_curl(Grid g, const Real* __restrict__ u, const Real* __restrict__ v, const Real* __restrict__ w,
                                               Real* __restrict__ cx, Real* __restrict__ cy, Real* __restrict__ cz) {
+    INK_PDL();
     int i, j, k; long long c;
     if (!cell_of_thread(g, (long long)blockIdx.x * blockDim.x + threadIdx.x, i, j, k, c)) return;
     const bool ip = i + 1 < g.X, im = i - 1 >= 0, jp = j + 1 < g.Y, jm = j - 1 >= 0, kp = k + 1 < g.Z, km = k - 1 >= 0;
@@ -336,6 +346,7 @@ template <class Real>
 __global__ void __launch_bounds__(256) k_vorticity(Grid g, Real dt, Real kvort, const Real* __restrict__ cx, const Real* __restrict__ cy,
                                                    const Real* __restrict__ cz, Real* __restrict__ u, Real* __restrict__ v, Real* __restrict__ w,
                                                    unsigned int* maxspeed) {
+    INK_PDL();
     int i, j, k; long long c;
     float speed = 0.f;
     if (cell_of_thread(g, (long long)blockIdx.x * blockDim.x + threadIdx.x, i, j, k, c)) {
@@ -369,6 +380,7 @@ __global__ void __launch_bounds__(256) k_vorticity(Grid g, Real dt, Real kvort, 
 // ------------------------------------------------------------------------------------------------
 template <class Tin, class Tout>
 __global__ void __launch_bounds__(256) k_xyz_to_internal(Grid g, const Tin* __restrict__ in, Tout* __restrict__ out) {
+    INK_PDL();
     const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= g.n) return;
     const int k = (int)(t % g.Z);
@@ -378,6 +390,7 @@ __global__ void __launch_bounds__(256) k_xyz_to_internal(Grid g, const Tin* __re
 }
 template <class Tin, class Tout>
 __global__ void __launch_bounds__(256) k_internal_to_xyz(Grid g, const Tin* __restrict__ in, Tout* __restrict__ out) {
+    INK_PDL();
     const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= g.n) return;
     const int k = (int)(t % g.Z);
@@ -386,6 +399,7 @@ __global__ void __launch_bounds__(256) k_internal_to_xyz(Grid g, const Tin* __re
     out[((long long)i * g.Y + j) * g.Z + k] = (Tout)in[t];
 }
 __global__ void __launch_bounds__(256) k_mark_to_xyz(Grid g, const uint8_t* __restrict__ in, uint8_t* __restrict__ out) {
+    INK_PDL();
     const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= g.n) return;
     const int k = (int)(t % g.Z);

@@ -173,18 +173,21 @@ constexpr int kMgBlocks = 148 * 8;
 
 template <class Real>
 __global__ void __launch_bounds__(256) k_mg_presmooth(const CgScal* S, MgDims d, Real s, const Real* __restrict__ r, Real* __restrict__ x) {
+    INK_PDL();
     if (S->done) return;
     mg_presmooth<Real>(d, s, r, x, (long long)blockIdx.x * blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x);
 }
 template <class Real>
 __global__ void __launch_bounds__(256) k_mg_residual_restrict(const CgScal* S, MgDims df, MgDims dc, Real s, const Real* __restrict__ r,
                                                               const Real* __restrict__ x, Real* __restrict__ rc) {
+    INK_PDL();
     if (S->done) return;
     mg_residual_restrict<Real>(df, dc, s, r, x, rc, (long long)blockIdx.x * blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x);
 }
 template <class Real>
 __global__ void __launch_bounds__(256) k_mg_prolong_smooth(const CgScal* S, MgDims df, MgDims dc, Real s, const Real* __restrict__ r,
                                                            const Real* __restrict__ xi, const Real* __restrict__ e, Real* __restrict__ xo) {
+    INK_PDL();
     if (S->done) return;
     mg_prolong_smooth<Real>(df, dc, s, r, xi, e, xo, (long long)blockIdx.x * blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x);
 }
@@ -192,6 +195,7 @@ __global__ void __launch_bounds__(256) k_mg_prolong_smooth(const CgScal* S, MgDi
 template <class Real, bool FINAL>
 __global__ void __launch_bounds__(256) k_mg_smooth(CgScal* S, MgDims d, Real s, const Real* __restrict__ r, const Real* __restrict__ xi, Real* __restrict__ xo,
                                                    int dj0, int dj1) {
+    INK_PDL();
     if (S->done) return;
     const double acc = mg_smooth<Real>(d, s, r, xi, xo, (long long)blockIdx.x * blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x, dj0, dj1);
     if (FINAL) {
@@ -213,6 +217,7 @@ struct MgTailArgs {
 
 template <class Real>
 __global__ void __launch_bounds__(kMgTailThreads) k_mg_tail(CgScal* S, MgTailArgs A, const Real* __restrict__ rin, Real* __restrict__ xout) {
+    INK_PDL();
     if (S->done) return;
     extern __shared__ __align__(16) unsigned char mg_smem_raw[];
     Real* sm = reinterpret_cast<Real*>(mg_smem_raw);

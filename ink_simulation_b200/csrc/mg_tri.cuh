@@ -276,12 +276,14 @@ INK_HD double mg3_up(const MgDims& df, const MgDims& dc, Real s, const Real* __r
 // ---- global-memory kernels ---------------------------------------------------------------------------------------
 template <class Real>
 __global__ void __launch_bounds__(256) k_mg3_residual(const CgScal* S, MgDims d, const Real* __restrict__ r, Real* __restrict__ res) {
+    INK_PDL();
     if (S->done) return;
     mg3_residual<Real>(d, r, res, (long long)blockIdx.x * blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x);
 }
 // Z % 4 == 0: one thread per 4 z-consecutive cells, 128-bit accesses (same arithmetic per cell)
 template <class Real>
 __global__ void __launch_bounds__(256) k_mg3_residual_v4(const CgScal* S, MgDims d, const Real* __restrict__ r, Real* __restrict__ res) {
+    INK_PDL();
     if (S->done) return;
     const Real w6 = Real(kMgOmega) / Real(6);
     int i, j, k; long long c;
@@ -297,6 +299,7 @@ __global__ void __launch_bounds__(256) k_mg3_residual_v4(const CgScal* S, MgDims
 }
 template <class Real>
 __global__ void __launch_bounds__(256) k_mg3_restrict(const CgScal* S, MgDims df, MgDims dc, const Real* __restrict__ res, Real* __restrict__ rc) {
+    INK_PDL();
     if (S->done) return;
     mg3_restrict<Real>(df, dc, res, rc, (long long)blockIdx.x * blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x);
 }
@@ -304,6 +307,7 @@ __global__ void __launch_bounds__(256) k_mg3_restrict(const CgScal* S, MgDims df
 template <class Real, bool FINAL>
 __global__ void __launch_bounds__(256) k_mg3_up(CgScal* S, MgDims df, MgDims dc, Real s, const Real* __restrict__ r, const Real* __restrict__ e,
                                                 Real* __restrict__ z, int dj0, int dj1) {
+    INK_PDL();
     if (S->done) return;
     const double acc = mg3_up<Real>(df, dc, s, r, e, z, (long long)blockIdx.x * blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x, dj0, dj1);
     if (FINAL) {
@@ -328,6 +332,7 @@ __device__ __forceinline__ Real mg3_res_at(const MgDims& d, const Real* __restri
 }
 template <class Real>
 __global__ void __launch_bounds__(256) k_mg3_residual_rz_v4(const CgScal* S, MgDims d, const Real* __restrict__ r, Real* __restrict__ resz) {
+    INK_PDL();
     if (S->done) return;
     const Real w6 = Real(kMgOmega) / Real(6);
     const unsigned int ZV = (unsigned int)d.Z >> 2;
@@ -361,6 +366,7 @@ __global__ void __launch_bounds__(256) k_mg3_residual_rz_v4(const CgScal* S, MgD
 // rc[I,J,K] = sum over the 4x4 fine columns (2I-1..2I+2, 2J-1..2J+2) of wx wy resz[.,.,K]
 template <class Real>
 __global__ void __launch_bounds__(256) k_mg3_restrict_xy(const CgScal* S, MgDims df, MgDims dc, const Real* __restrict__ resz, Real* __restrict__ rc) {
+    INK_PDL();
     if (S->done) return;
     INK_MG_CELL_LOOP(dc, (long long)blockIdx.x * blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x) {
         INK_MG_DECODE(dc)
@@ -386,6 +392,7 @@ __global__ void __launch_bounds__(256) k_mg3_restrict_xy(const CgScal* S, MgDims
 // ---- shared-memory tail: all levels from `lt` down in ONE block (MgTailArgs of mg.cuh; 3 arrays per level) ----------
 template <class Real>
 __global__ void __launch_bounds__(kMgTailThreads) k_mg3_tail(CgScal* S, MgTailArgs A, const Real* __restrict__ rin, Real* __restrict__ xout) {
+    INK_PDL();
     if (S->done) return;
     extern __shared__ __align__(16) unsigned char mg_smem_raw[];
     Real* sm = reinterpret_cast<Real*>(mg_smem_raw);

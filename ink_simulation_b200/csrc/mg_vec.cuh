@@ -52,6 +52,7 @@ __device__ __forceinline__ void mg_lap4(const MgDims& d, const Real* __restrict_
 
 template <class Real>
 __global__ void __launch_bounds__(256) k_mg_presmooth_v4(const CgScal* S, MgDims d, Real s, const Real* __restrict__ r, Real* __restrict__ x) {
+    INK_PDL();
     if (S->done) return;
     const Real cj = Real(kMgOmega) / (Real(6) * s), w6 = Real(kMgOmega) / Real(6);
     int i, j, k; long long c;
@@ -69,6 +70,7 @@ __global__ void __launch_bounds__(256) k_mg_presmooth_v4(const CgScal* S, MgDims
 template <class Real, bool FINAL>
 __global__ void __launch_bounds__(256) k_mg_smooth_v4(CgScal* S, MgDims d, Real s, const Real* __restrict__ r, const Real* __restrict__ xi, Real* __restrict__ xo,
                                                       int dj0, int dj1) {
+    INK_PDL();
     if (S->done) return;
     const Real cj = Real(kMgOmega) / (Real(6) * s);
     int i, j, k; long long c;
@@ -98,6 +100,7 @@ __global__ void __launch_bounds__(256) k_mg_smooth_v4(CgScal* S, MgDims d, Real 
 template <class Real>
 __global__ void __launch_bounds__(256) k_mg_prolong_smooth_v4(const CgScal* S, MgDims df, MgDims dc, Real s, const Real* __restrict__ r,
                                                               const Real* __restrict__ xi, const Real* __restrict__ e, Real* __restrict__ xo) {
+    INK_PDL();
     if (S->done) return;
     const Real cj = Real(kMgOmega) / (Real(6) * s);
     const long long sx = df.Z, sy = (long long)df.X * df.Z;
@@ -142,6 +145,7 @@ __global__ void __launch_bounds__(256) k_mg_prolong_smooth_v4(const CgScal* S, M
 template <class Real>
 __global__ void __launch_bounds__(256) k_mg_residual_restrict_v4(const CgScal* S, MgDims df, MgDims dc, Real s, const Real* __restrict__ r,
                                                                  const Real* __restrict__ x, Real* __restrict__ rc) {
+    INK_PDL();
     if (S->done) return;
     const unsigned int ZV = (unsigned int)dc.Z >> 1;   // df.Z % 4 == 0  =>  dc.Z even
     const unsigned int tot = (unsigned int)(dc.j1 - dc.j0) * (unsigned int)dc.X * ZV;
@@ -181,6 +185,7 @@ __global__ void __launch_bounds__(256) k_mg_residual_restrict_v4(const CgScal* S
 template <class Real>
 __global__ void __launch_bounds__(256) k_band_scale(const CgScal* S, long long sy, int ja, int jb, int own0, int own1, const Real* __restrict__ sw,
                                                     Real* __restrict__ r, Real* __restrict__ save) {
+    INK_PDL();
     if (S->done) return;
     const long long n = (long long)(jb - ja) * sy;
     for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) {
@@ -194,6 +199,7 @@ __global__ void __launch_bounds__(256) k_band_scale(const CgScal* S, long long s
 template <class Real>
 __global__ void __launch_bounds__(256) k_band_restore_weight(const CgScal* S, long long sy, int ja, int jb, int own0, int own1, const Real* __restrict__ sw,
                                                              Real* __restrict__ r, const Real* __restrict__ save, Real* __restrict__ z) {
+    INK_PDL();
     if (S->done) return;
     const long long n = (long long)(jb - ja) * sy;
     for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) {
@@ -207,6 +213,7 @@ __global__ void __launch_bounds__(256) k_band_restore_weight(const CgScal* S, lo
 template <class Real>
 __global__ void __launch_bounds__(256) k_band_combine(CgScal* S, long long sy, int ja, int jb, int own0, int own1, const Real* __restrict__ recv,
                                                       const Real* __restrict__ r, Real* __restrict__ z) {
+    INK_PDL();
     if (S->done) return;
     const long long n = (long long)(jb - ja) * sy;
     double acc = 0;

@@ -44,6 +44,7 @@ template <class Real, bool FAST, bool UNIT_H>
 __global__ void __launch_bounds__(256) k_particles_rk2(Grid g, Consts<Real> C, Real dt, long long n, Particles<Real> P,
                                                        const Real* __restrict__ u, const Real* __restrict__ v, const Real* __restrict__ w,
                                                        uint8_t* __restrict__ seed) {
+    INK_PDL();
     const long long s = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n) return;
     Real x = ld_stream(P.p[0] + s), y = ld_stream(P.p[1] + s), z = ld_stream(P.p[2] + s);
@@ -72,6 +73,7 @@ __global__ void __launch_bounds__(256) k_particles_rk2(Grid g, Consts<Real> C, R
 // K2a stand-alone: seed mask from the current positions (after ink_set_particles); counts out-of-grid particles.
 template <class Real>
 __global__ void __launch_bounds__(256) k_mark_particle_cells(Grid g, long long n, Particles<Real> P, uint8_t* __restrict__ seed, unsigned int* oob_count) {
+    INK_PDL();
     const long long s = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n) return;
     long long c;
@@ -83,6 +85,7 @@ __global__ void __launch_bounds__(256) k_mark_particle_cells(Grid g, long long n
 template <class Real, bool FAST>
 __global__ void __launch_bounds__(256) k_sample(Grid g, Consts<Real> C, long long n, const Real* __restrict__ pos, Real* __restrict__ out,
                                                 const Real* __restrict__ u, const Real* __restrict__ v, const Real* __restrict__ w) {
+    INK_PDL();
     const long long s = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n) return;
     Real a, b, c;
@@ -95,6 +98,7 @@ __global__ void __launch_bounds__(256) k_sample(Grid g, Consts<Real> C, long lon
 // ------------------------------------------------------------------------------------------------
 template <class Tin, class Real>
 __global__ void __launch_bounds__(256) k_import_aos(long long n, long long dst_off, const Tin* __restrict__ pos, const Tin* __restrict__ vel, Particles<Real> P) {
+    INK_PDL();
     const long long s = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n) return;
     const long long d = dst_off + s;
@@ -109,6 +113,7 @@ __global__ void __launch_bounds__(256) k_import_aos(long long n, long long dst_o
 // already occupy (orig keeps the mapping).  No re-binning, velocities untouched (K8 overwrites them).
 template <class Tin, class Real>
 __global__ void __launch_bounds__(256) k_import_pos_perm(long long n, long long off, long long cnt, Particles<Real> P, const Tin* __restrict__ pos) {
+    INK_PDL();
     const long long s = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n) return;
     const long long o = (long long)P.orig[s] - off;
@@ -119,6 +124,7 @@ __global__ void __launch_bounds__(256) k_import_pos_perm(long long n, long long 
 // out[(orig - off)*3 + a] for the particles of one drop (orig in [off, off+cnt))
 template <class Real, class Tout>
 __global__ void __launch_bounds__(256) k_export_aos(long long n, long long off, long long cnt, Particles<Real> P, Tout* __restrict__ pos, Tout* __restrict__ vel) {
+    INK_PDL();
     const long long s = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n) return;
     const long long o = (long long)P.orig[s] - off;
@@ -139,6 +145,7 @@ __device__ __forceinline__ uint32_t bin_key(const Grid& g, Real x, Real y, Real 
 }
 template <class Real>
 __global__ void __launch_bounds__(256) k_bin_count(Grid g, long long n, Particles<Real> P, uint32_t* __restrict__ count, uint32_t* __restrict__ key, uint32_t* __restrict__ rank) {
+    INK_PDL();
     const long long s = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n) return;
     const uint32_t c = bin_key(g, P.p[0][s], P.p[1][s], P.p[2][s]);
@@ -148,6 +155,7 @@ __global__ void __launch_bounds__(256) k_bin_count(Grid g, long long n, Particle
 template <class Real>
 __global__ void __launch_bounds__(256) k_bin_scatter(long long n, Particles<Real> src, Particles<Real> dst, const uint32_t* __restrict__ offset,
                                                      const uint32_t* __restrict__ key, const uint32_t* __restrict__ rank) {
+    INK_PDL();
     const long long s = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n) return;
     const long long d = (long long)offset[key[s]] + rank[s];
@@ -158,7 +166,8 @@ __global__ void __launch_bounds__(256) k_bin_scatter(long long n, Particles<Real
 
 // ---- exclusive scan of uint32 (tile = 256 threads x 8) ------------------------------------------
 constexpr int kScanTile = 2048;
-__global__ void __launch_bounds__(256) k_scan_tiles(long long n, const uint32_t* in, uint32_t* out, uint32_t* __restrict__ tilesum) {  // in may alias out
+__global__ void __launch_bounds__(256) k_scan_tiles(long long n, const uint32_t* in, uint32_t* out, uint32_t* __restrict__ tilesum) {
+    INK_PDL();  // in may alias out
     __shared__ uint32_t wsum[8];
     const long long base = (long long)blockIdx.x * kScanTile + (long long)threadIdx.x * 8;
     uint32_t v[8], t = 0;
@@ -179,6 +188,7 @@ __global__ void __launch_bounds__(256) k_scan_tiles(long long n, const uint32_t*
     if (threadIdx.x == 255) tilesum[blockIdx.x] = woff + inc;
 }
 __global__ void __launch_bounds__(256) k_scan_add(long long n, uint32_t* __restrict__ out, const uint32_t* __restrict__ tileoff) {
+    INK_PDL();
     const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (t < n) out[t] += tileoff[t / kScanTile];
 }
