@@ -255,8 +255,9 @@ struct Ctx final : CtxBase {
         CK(cudaMalloc(&d_scal, 4 * sizeof(unsigned int))); CK(cudaMemsetAsync(d_scal, 0, 4 * sizeof(unsigned int), stream));
         CK(cudaMallocHost(&h_scal, 4 * sizeof(unsigned int)));
         // counting-sort scratch: per-cell counts + scan levels
-        CK(cudaMalloc(&bin_count, (size_t)g.n * sizeof(uint32_t)));
-        long long m = g.n;
+        if ((long long)kBinsPerCell * g.n >= (1ll << 32)) { err = "grid too large for 32-bit particle bin keys"; return 2; }
+        CK(cudaMalloc(&bin_count, (size_t)kBinsPerCell * g.n * sizeof(uint32_t)));
+        long long m = kBinsPerCell * g.n;
         while (m > 1) {
             m = (m + kScanTile - 1) / kScanTile;
             uint32_t* lvl;
@@ -354,7 +355,7 @@ struct Ctx final : CtxBase {
     bool vec4() const { return (g.Z % 4) == 0; }
     unsigned int cg_blocks() const {
         const long long nvec = (long long)(g.j1 - g.j0) * g.X * (g.Z / (vec4() ? 4 : 1));
-        return (unsigned int)std::min<long long>(kCgMaxBlocks, std::max<long long>(1, (nvec + 255) / 256));
+        return (unsigned int)std::min<long long>(kCgBlocks, std::max<long long>(1, (nvec + 255) / 256));
     }
 
     template <class T>
@@ -588,7 +589,7 @@ struct Ctx final : CtxBase {
     }
 
     int scan_counts() {   // exclusive scan of bin_count in place
-        long long m = g.n;
+        long long m = kBinsPerCell * g.n;
         uint32_t* in = bin_count;
         size_t lvl = 0;
         std::vector<uint32_t*> ins;
@@ -607,7 +608,7 @@ struct Ctx final : CtxBase {
     int resort() override {
         since_sort = 0;
         if (np == 0) return 0;
-        CK(cudaMemsetAsync(bin_count, 0, (size_t)g.n * sizeof(uint32_t), stream));
+        CK(cudaMemsetAsync(bin_count, 0, (size_t)kBinsPerCell * g.n * sizeof(uint32_t), stream));
         LAUNCH((k_bin_count<Real>), nblk(np), 256, g, np, part[pcur], bin_count, bin_key, bin_rank);
         if (int rc = scan_counts()) return rc;
         LAUNCH((k_bin_scatter<Real>), nblk(np), 256, np, part[pcur], part[pcur ^ 1], bin_count, bin_key, bin_rank);
@@ -905,7 +906,10 @@ struct Ctx final : CtxBase {
                 if (df.Z % 4 == 0 && mg_fuse) {   // residual + z-restriction fused (xb holds the half-size z-restricted residual)
                     const long long nv = (long long)df.X * (df.j1 - df.j0) * (df.Z / 4);
                     LAUNCH((k_mg3_residual_rz_v4<Real>), (unsigned int)std::min<long long>(kMgBlocks, std::max<long long>(1, (nv + 255) / 256)), 256, S, df, rhs(l), lv[l].xb);
-                    LAUNCH((k_mg3_restrict_xy<Real>), mg_blocks(dc), 256, S, df, dc, lv[l].xb, lv[l + 1].r);
+                    if (dc.Z % 4 == 0) {
+                        const long long nc4 = (long long)dc.X * (dc.j1 - dc.j0) * (dc.Z / 4);
+                        LAUNCH((k_mg3_restrict_xy_v4<Real>), (unsigned int)std::min<long long>(kMgBlocks, std::max<long long>(1, (nc4 + 255) / 256)), 256, S, df, dc, lv[l].xb, lv[l + 1].r);
+                    } else LAUNCH((k_mg3_restrict_xy<Real>), mg_blocks(dc), 256, S, df, dc, lv[l].xb, lv[l + 1].r);
                     continue;
                 }
                 if (df.Z % 4 == 0) {
@@ -922,8 +926,12 @@ struct Ctx final : CtxBase {
             }
             for (int l = mg_lt - 1; l >= 0; --l) {
                 const MgDims &df = lv[l].d, &dc = lv[l + 1].d;
-                if (l == 0) LAUNCH((k_mg3_up<Real, true>), mg_blocks(dc), 256, S, df, dc, lv[l].s, rhs(l), lv[l + 1].xa, lv[l].xa, dot0, dot1);
-                else LAUNCH((k_mg3_up<Real, false>), mg_blocks(dc), 256, S, df, dc, lv[l].s, rhs(l), lv[l + 1].xa, lv[l].xa, 0, 0);
+                // one coarse cell per thread, no grid-stride tail (a thread's work is ~700 instructions); the fp64 partials of
+                // block_sum_last cap the FINAL launch at kCgMaxBlocks blocks
+                const long long ncc = (long long)dc.X * (dc.j1 - dc.j0) * dc.Z;
+                const unsigned int ub = (unsigned int)std::max<long long>(1, (ncc + 255) / 256);
+                if (l == 0) LAUNCH((k_mg3_up<Real, true>), std::min<unsigned int>(ub, kCgMaxBlocks), 256, S, df, dc, lv[l].s, rhs(l), lv[l + 1].xa, lv[l].xa, dot0, dot1);
+                else LAUNCH((k_mg3_up<Real, false>), ub, 256, S, df, dc, lv[l].s, rhs(l), lv[l + 1].xa, lv[l].xa, 0, 0);
             }
             CK(cudaGetLastError());
             return 0;

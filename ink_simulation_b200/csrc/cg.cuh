@@ -16,7 +16,8 @@
 
 namespace ink {
 
-constexpr int kCgMaxBlocks = 148 * 8;
+constexpr int kCgBlocks = 148 * 8;       // grid of the CG kernels (grid-stride)
+constexpr int kCgMaxBlocks = 148 * 32;   // capacity of the per-block fp64 partials (largest grid any reducing kernel may use)
 
 struct CgScal {
     double rr, rr_old, dw, bb, tol2;

@@ -99,8 +99,10 @@ INK_HD double mg3_up_cell_fast(const MgDims& df, const MgDims& dc, Real cj, cons
                                int I, int J, int K, int dj0, int dj1) {
     const Real a0 = Real(1) - Real(kMgOmega), a1 = Real(kMgOmega) / Real(6), sc = Real(1) / Real(64);
     const bool zlo = K > 0, zhi = K + 1 < dc.Z;
-    const long long sxc = dc.Z, syc = (long long)dc.X * dc.Z, sxf = df.Z, syf = (long long)df.X * df.Z;
-    const Real* __restrict__ eb = e + mg_idx(dc, I - 1, J - 1, K);
+    // 32-bit element offsets (a level has < 2^31 cells): one IMAD.WIDE per access instead of 64-bit index arithmetic,
+    // which was 40 % of this kernel's instructions (profiles/r1_c_mg3_up.txt)
+    const int sxc = dc.Z, syc = dc.X * dc.Z, sxf = df.Z, syf = df.X * df.Z;
+    const Real* __restrict__ eb = e + (((J - 1) * dc.X + (I - 1)) * dc.Z + K);
     Real tz[3][3][4];
 #pragma unroll
     for (int a = 0; a < 3; ++a)
@@ -121,7 +123,7 @@ INK_HD double mg3_up_cell_fast(const MgDims& df, const MgDims& dc, Real cj, cons
             for (int n = 0; n < 4; ++n) ty[a][n][m] = o[n];
         }
     Real xp[4][4][4], rin[2][2][2];
-    const long long fb = mg_idx(df, 2 * I - 1, 2 * J - 1, 2 * K);
+    const int fb = ((2 * J - 1) * df.X + (2 * I - 1)) * df.Z + 2 * K;
 #pragma unroll
     for (int n = 0; n < 4; ++n)
 #pragma unroll
@@ -150,6 +152,7 @@ INK_HD double mg3_up_cell_fast(const MgDims& df, const MgDims& dc, Real cj, cons
     for (int n = 1; n < 3; ++n) {
         const int fj = 2 * J - 1 + n;
         const bool in_dot = (fj >= dj0) && (fj < dj1);
+        Real dsum = Real(0);   // the 4 products of one fine row in working precision, then one fp64 add
 #pragma unroll
         for (int l = 1; l < 3; ++l) {
             Pack<Real, 2> o;
@@ -159,10 +162,11 @@ INK_HD double mg3_up_cell_fast(const MgDims& df, const MgDims& dc, Real cj, cons
                 const Real rr = rin[l - 1][n - 1][m - 1];
                 const Real v = hd_fma(a1, nb, hd_fma(a0, xp[l][n][m], cj * rr));
                 o.a[m - 1] = v;
-                if (in_dot) acc += (double)rr * (double)v;
+                dsum = hd_fma(rr, v, dsum);
             }
             stp<Real, 2>(z + fb + l * sxf + n * syf, o);
         }
+        if (in_dot) acc += (double)dsum;
     }
     return acc;
 }
@@ -305,7 +309,7 @@ __global__ void __launch_bounds__(256) k_mg3_restrict(const CgScal* S, MgDims df
 }
 // FINAL: level 0 — also produces <r, z> for CG (rz_old <- rz, rz <- <r,z>)
 template <class Real, bool FINAL>
-__global__ void __launch_bounds__(256) k_mg3_up(CgScal* S, MgDims df, MgDims dc, Real s, const Real* __restrict__ r, const Real* __restrict__ e,
+__global__ void __launch_bounds__(256, 3) k_mg3_up(CgScal* S, MgDims df, MgDims dc, Real s, const Real* __restrict__ r, const Real* __restrict__ e,
                                                 Real* __restrict__ z, int dj0, int dj1) {
     INK_PDL();
     if (S->done) return;
@@ -386,6 +390,37 @@ __global__ void __launch_bounds__(256) k_mg3_restrict_xy(const CgScal* S, MgDims
             acc += wy * a;
         }
         rc[c] = acc;
+    }
+}
+
+// same, coarse Z % 4 == 0: one thread per 4 z-consecutive coarse cells, 16 LDG.128 + 1 STG.128 (the scalar kernel is
+// issue-bound on index arithmetic and validity tests: 62 % issue slots at 7 % of DRAM peak, profiles/r1_c_mg3_down.txt)
+template <class Real>
+__global__ void __launch_bounds__(256) k_mg3_restrict_xy_v4(const CgScal* S, MgDims df, MgDims dc, const Real* __restrict__ resz, Real* __restrict__ rc) {
+    INK_PDL();
+    if (S->done) return;
+    int i, j, k; long long c;
+    for (unsigned int t = blockIdx.x * blockDim.x + threadIdx.x; mg_vec_cell(dc, t, i, j, k, c); t += gridDim.x * blockDim.x) {
+        Real acc[4] = {Real(0), Real(0), Real(0), Real(0)};
+#pragma unroll
+        for (int n = 0; n < 4; ++n) {
+            const int fj = 2 * j - 1 + n;
+            if (fj < df.j0 || fj >= df.j1) continue;
+            const Real wy = (n == 1 || n == 2) ? Real(0.75) : Real(0.25);
+#pragma unroll
+            for (int l = 0; l < 4; ++l) {
+                const int fi = 2 * i - 1 + l;
+                if (fi < 0 || fi >= df.X) continue;
+                const Real w = wy * ((l == 1 || l == 2) ? Real(0.75) : Real(0.25));
+                const P4<Real> q = ldp<Real, 4>(resz + ((long long)fj * df.X + fi) * dc.Z + k);
+#pragma unroll
+                for (int a = 0; a < 4; ++a) acc[a] = hd_fma(w, q.a[a], acc[a]);
+            }
+        }
+        P4<Real> o;
+#pragma unroll
+        for (int a = 0; a < 4; ++a) o.a[a] = acc[a];
+        stp<Real, 4>(rc + c, o);
     }
 }
 

@@ -136,12 +136,19 @@ __global__ void __launch_bounds__(256) k_export_aos(long long n, long long off, 
     }
 }
 
-// bin key = internal cell index of the (clamped) position
+// bin key: particles are binned by QUARTER COLUMN — the half-cell the position falls in along x and y, then the cell
+// along z:  key = ((2j + hy) * 2X + (2i + hx)) * Z + k,  hx = frac(x) >= 0.5.  The staggered sampler reads rows
+// floor(x), floor(x - 0.5), floor(y), floor(y - 0.5): inside one quarter column all four are the same for every
+// particle, so each of a warp's 48 corner gathers falls in ONE z-row of the field (1-3 128-byte lines) instead of the
+// 2 (u, v) or 4 (w) rows a whole-cell bin mixes (ncu r1_b: 3.0 L1 wavefronts per gather, the kernel's bottleneck).
+constexpr int kBinsPerCell = 4;
 template <class Real>
 __device__ __forceinline__ uint32_t bin_key(const Grid& g, Real x, Real y, Real z) {
-    int i = (int)rfloor(x), j = (int)rfloor(y), k = (int)rfloor(z);
-    i = min(max(i, 0), g.X - 1); j = min(max(j, 0), g.Y - 1); k = min(max(k, 0), g.Z - 1);
-    return (uint32_t)cidx(g, i, j, k);
+    const Real fx = rfloor(x), fy = rfloor(y);
+    int i = (int)fx, j = (int)fy, k = (int)rfloor(z);
+    const int hx = (x - fx >= Real(0.5)) ? 1 : 0, hy = (y - fy >= Real(0.5)) ? 1 : 0;
+    i = min(max(2 * i + hx, 0), 2 * g.X - 1); j = min(max(2 * j + hy, 0), 2 * g.Y - 1); k = min(max(k, 0), g.Z - 1);
+    return (uint32_t)(((long long)j * (2 * g.X) + i) * g.Z + k);
 }
 template <class Real>
 __global__ void __launch_bounds__(256) k_bin_count(Grid g, long long n, Particles<Real> P, uint32_t* __restrict__ count, uint32_t* __restrict__ key, uint32_t* __restrict__ rank) {
