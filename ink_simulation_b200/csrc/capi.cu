@@ -249,6 +249,7 @@ struct Ctx final : CtxBase {
         for (Real** ptr : {&pres, &q, &rhs, &cg_r, &cg_d[0], &cg_d[1], &cg_w}) { CK(cudaMalloc(ptr, nb)); CK(cudaMemsetAsync(*ptr, 0, nb, stream)); }
         CK(cudaMalloc(&S, sizeof(CgScal))); CK(cudaMemsetAsync(S, 0, sizeof(CgScal), stream));
         { const int dist = world > 1; CK(cudaMemcpyAsync(&S->dist, &dist, sizeof(int), cudaMemcpyHostToDevice, stream)); }
+        { const double tol2 = P.cg_rtol * P.cg_rtol; CK(cudaMemcpyAsync(&S->tol2, &tol2, sizeof(double), cudaMemcpyHostToDevice, stream)); CK(cudaStreamSynchronize(stream)); }
         CK(cudaMallocHost(&hS, sizeof(CgScal)));
         CK(cudaMalloc(&seed, g.n)); CK(cudaMemsetAsync(seed, 0, g.n, stream));
         CK(cudaMalloc(&mark, g.n)); CK(cudaMemsetAsync(mark, 0, g.n, stream));
@@ -277,6 +278,11 @@ struct Ctx final : CtxBase {
     }
 
     // ---- helpers ---------------------------------------------------------------------------------
+    // device -> pinned host, a few words, by a kernel instead of the D2H copy engine (see k_copy_words)
+    void read_small(void* host_pinned, const void* dev, size_t bytes) {
+        launch_k(k_copy_words, 1, 64, 0, stream, (uint32_t*)host_pinned, (const uint32_t*)dev, (int)(bytes / 4));
+        ++stats.kernel_launches;
+    }
     static bool is_device_ptr(const void* p) {
         cudaPointerAttributes a;
         if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
@@ -632,7 +638,7 @@ struct Ctx final : CtxBase {
         if (int rc = allreduce(d_scal + 1, 1, ncclUint32, ncclSum)) return rc;
         if (int rc = allreduce(seed, (size_t)g.n, ncclUint8, ncclMax)) return rc;   // OR of every rank's particle cells
         seed_global = true;
-        CK(cudaMemcpyAsync(h_scal + 1, d_scal + 1, sizeof(unsigned int), cudaMemcpyDeviceToHost, stream));
+        read_small(h_scal + 1, d_scal + 1, sizeof(unsigned int));
         CK(cudaStreamSynchronize(stream));
         oob_now = h_scal[1] > 0;
         if (oob_now) have_phantom = true;
@@ -726,7 +732,7 @@ struct Ctx final : CtxBase {
             if (int rc = allreduce(d_scal, 1, ncclUint32, ncclMax)) return rc;   // non-negative floats order like their bits
             maxv_valid = true;
         }
-        CK(cudaMemcpyAsync(h_scal, d_scal, sizeof(unsigned int), cudaMemcpyDeviceToHost, stream));
+        read_small(h_scal, d_scal, sizeof(unsigned int));
         CK(cudaStreamSynchronize(stream));
         float m;
         memcpy(&m, h_scal, 4);
@@ -1015,8 +1021,6 @@ struct Ctx final : CtxBase {
         const unsigned int nb = cg_blocks();
         const bool dist = world > 1;
         const int hlo = (dist && rank > 0) ? 1 : 0, hhi = (dist && rank + 1 < world) ? 1 : 0;
-        const double tol2 = P.cg_rtol * P.cg_rtol;
-        CK(cudaMemcpyAsync(&S->tol2, &tol2, sizeof(double), cudaMemcpyHostToDevice, stream));
         if (int rc = halo_exchange(x, 1, 1)) return rc;     // warm start: the initial residual needs x on the neighbour rows
         if (vec4()) LAUNCH((k_cg_init<Real, 4>), nb, 256, g, S, f, x, cg_r);
         else LAUNCH((k_cg_init<Real, 1>), nb, 256, g, S, f, x, cg_r);
@@ -1026,7 +1030,7 @@ struct Ctx final : CtxBase {
             cg_post(0);
         }
         const size_t head = offsetof(CgScal, partial);
-        CK(cudaMemcpyAsync(hS, S, head, cudaMemcpyDeviceToHost, stream));
+        read_small(hS, S, head);
         CK(cudaStreamSynchronize(stream));
         if (hS->bb == 0.0) {  // f == 0: the solution is exactly 0
             CK(cudaMemsetAsync(x, 0, (size_t)g.n * sizeof(Real), stream));
@@ -1075,7 +1079,7 @@ struct Ctx final : CtxBase {
             }
             launched += batch;
             CK(cudaGetLastError());
-            CK(cudaMemcpyAsync(hS, S, head, cudaMemcpyDeviceToHost, stream));
+            read_small(hS, S, head);
             CK(cudaStreamSynchronize(stream));
         }
         prev_iters = hS->iters;

@@ -251,6 +251,16 @@ __global__ void __launch_bounds__(256) k_cg_update(Grid g, CgScal* S, Real* __re
     }
 }
 
+// Small device -> pinned-host readback WITHOUT the copy engine: one warp stores the words straight into mapped host memory
+// (UVA: a cudaMallocHost pointer is valid on the device).  The step's host-visible scalars (dt, CG convergence head, out-of-
+// grid particle count) used to go through cudaMemcpyAsync on the compute stream, i.e. through the D2H copy engine, where they
+// queued behind a 120 MB particle download running on the output copy stream: the whole step then waited for that copy.
+__global__ void k_copy_words(uint32_t* __restrict__ dst_host, const uint32_t* __restrict__ src, int nwords) {
+    INK_PDL();
+    for (int t = threadIdx.x; t < nwords; t += blockDim.x) dst_host[t] = src[t];
+    __threadfence_system();
+}
+
 // Multi-GPU only: after ncclAllReduce(sum) of S->loc, one thread applies the global sums exactly like the fused single-GPU
 // epilogues do.  stage 0: after k_cg_init; 1: after k_cg_dir_matvec; 2: end of iteration (rr from k_cg_update, rz from the
 // V-cycle when preconditioned, else rz = rr); 3: <r,z> of the very first V-cycle.
