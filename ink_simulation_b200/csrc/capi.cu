@@ -20,6 +20,7 @@
 #include "mg.cuh"
 #include "mg_vec.cuh"
 #include "mg_tri.cuh"
+#include "p2p.cuh"
 #include "nccl_shim.h"
 #include "particle_kernels.cuh"
 
@@ -142,6 +143,30 @@ struct Ctx final : CtxBase {
     Real* band_recv[2] = {nullptr, nullptr};
     CgScal* S = nullptr;
     CgScal* hS = nullptr;  // pinned mirror of the scalar head
+    // multi-GPU: per-iteration exchanges by peer stores over NVLink (p2p.cuh) instead of NCCL calls
+    bool p2p = false;
+    // INK_TRACE_ITER=k: CUDA-event timeline of CG iteration k of every solve, printed by rank 0 (diagnostic)
+    int trace_iter = -1; bool tracing = false;
+    std::vector<cudaEvent_t> tr_ev; std::vector<const char*> tr_name;
+    void TR(const char* name) {
+        if (!tracing) return;
+        cudaEvent_t e; cudaEventCreate(&e); cudaEventRecord(e, stream); tr_ev.push_back(e); tr_name.push_back(name);
+    }
+    void tr_dump() {
+        if (tr_ev.empty()) return;
+        cudaStreamSynchronize(stream);
+        if (rank == 0) {
+            fprintf(stderr, "[inkb200 trace] iteration %d:", trace_iter);
+            for (size_t a = 1; a < tr_ev.size(); ++a) { float ms = 0; cudaEventElapsedTime(&ms, tr_ev[a - 1], tr_ev[a]); fprintf(stderr, " %s %.1f us |", tr_name[a], ms * 1e3f); }
+            fprintf(stderr, "\n");
+        }
+        for (auto e : tr_ev) cudaEventDestroy(e);
+        tr_ev.clear(); tr_name.clear();
+    }
+    unsigned char* arena = nullptr;
+    P2pPeers peers{};
+    size_t off_halo[2] = {0, 0}, off_band[2] = {0, 0};   // payload regions: [0] written by rank-1, [1] by rank+1
+    unsigned long long p2p_seq[2] = {0, 0};              // host sequence numbers of channel 0 (r halo) and 1 (z band)
     uint8_t *seed = nullptr, *mark = nullptr;
     unsigned int* d_scal = nullptr;  // [0] max speed bits, [1] oob particle count
     unsigned int* h_scal = nullptr;  // pinned
@@ -174,6 +199,9 @@ struct Ctx final : CtxBase {
     int in_next = 0, out_next = 0, in_pending = -1, in_pending_drop = -1, in_pending_hd = 32;
 
     ~Ctx() override {
+        for (int r = 0; r < world && r < kP2pMaxRanks; ++r)
+            if (p2p && r != rank && peers.base[r]) cudaIpcCloseMemHandle(peers.base[r]);
+        cudaFree(arena);
         if (comm) nccl().CommDestroy(comm);
         for (auto& b : vel)
             for (auto& p : b) cudaFree(p);
@@ -271,9 +299,89 @@ struct Ctx final : CtxBase {
             mg_tri = (P.cg_precond == INK_PCG_MG_TRI);
             if (int rc = mg_setup()) return rc;
         }
+        if (world > 1)
+            if (int rc = p2p_setup()) return rc;
         maxv_valid = true;  // zero field: max speed bits already 0
         seed_valid = true;
         CK(cudaStreamSynchronize(stream));
+        return 0;
+    }
+
+    // ---- peer-memory exchanges (p2p.cuh) ------------------------------------------------------------
+    // One arena per rank (mailboxes, flags, boundary-band payloads), exported over CUDA IPC; the handles travel once through
+    // ncclAllGather.  Any failure (no peer access, odd row size, INK_NO_P2P=1) leaves p2p == false: the NCCL path is kept.
+    int p2p_setup() {
+        if (const char* e = getenv("INK_NO_P2P")) if (atoi(e) != 0) return 0;
+        if (world > kP2pMaxRanks) return 0;
+        const size_t rowb = (size_t)g.sy * sizeof(Real);
+        if (rowb % 16 != 0) return 0;
+        const size_t head = (sizeof(P2pHead) + 255) / 256 * 256;
+        const size_t halo = (size_t)ovl * rowb, band = (size_t)2 * ovl * rowb;
+        off_halo[0] = head; off_halo[1] = head + halo;
+        off_band[0] = head + 2 * halo; off_band[1] = head + 2 * halo + band;
+        const size_t bytes = head + 2 * halo + 2 * band;
+        CK(cudaMalloc(&arena, bytes));
+        CK(cudaMemset(arena, 0, bytes));
+        cudaIpcMemHandle_t mine;
+        CK(cudaIpcGetMemHandle(&mine, arena));
+        static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+        unsigned char* hbuf = nullptr;
+        CK(cudaMalloc(&hbuf, (size_t)world * 64));
+        CK(cudaMemcpy(hbuf + (size_t)rank * 64, &mine, 64, cudaMemcpyHostToDevice));
+        NK(nccl().AllGather(hbuf + (size_t)rank * 64, hbuf, 64, ncclUint8, comm, stream));
+        CK(cudaStreamSynchronize(stream));
+        std::vector<cudaIpcMemHandle_t> all((size_t)world);
+        CK(cudaMemcpy(all.data(), hbuf, (size_t)world * 64, cudaMemcpyDeviceToHost));
+        cudaFree(hbuf);
+        int ok = 1;
+        for (int r = 0; r < world; ++r) {
+            if (r == rank) { peers.base[r] = arena; continue; }
+            void* ptr = nullptr;
+            if (cudaIpcOpenMemHandle(&ptr, all[(size_t)r], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); ok = 0; break; }
+            peers.base[r] = (unsigned char*)ptr;
+        }
+        // all ranks must agree (a rank that could not map a peer forces everybody back to NCCL)
+        int* dok = nullptr;
+        CK(cudaMalloc(&dok, sizeof(int)));
+        CK(cudaMemcpy(dok, &ok, sizeof(int), cudaMemcpyHostToDevice));
+        NK(nccl().AllReduce(dok, dok, 1, ncclInt32, ncclMin, comm, stream));
+        CK(cudaStreamSynchronize(stream));
+        CK(cudaMemcpy(&ok, dok, sizeof(int), cudaMemcpyDeviceToHost));
+        cudaFree(dok);
+        p2p = ok != 0;
+        if (rank == 0 && getenv("INK_VERBOSE")) fprintf(stderr, "[inkb200] world %d: per-iteration exchanges over %s\n", world, p2p ? "peer memory (CUDA IPC + NVLink stores)" : "NCCL");
+        return 0;
+    }
+    P2pHead* head_of(int r) const { return reinterpret_cast<P2pHead*>(peers.base[r]); }
+    // sum S->loc[off .. off+count) over the ranks, then the scalar epilogue `stage` of k_cg_post
+    int ar_post(int off, int count, int stage) {
+        if (p2p) {
+            launch_k(k_p2p_allreduce_post, 1, 32, 0, stream, S, peers, rank, world, off, count, stage, use_mg ? 1 : 0);
+            ++stats.kernel_launches;
+            return 0;
+        }
+        if (int rc = allreduce(S->loc + off, (size_t)count, ncclDouble, ncclSum)) return rc;
+        return cg_post(stage);
+    }
+    // channel ch: send rows [lo_src, +rows) to rank-1 and [hi_src, +rows) to rank+1 (into their regions at `off`), then wait for
+    // the neighbours' rows and (dst != nullptr) unpack them at lo_dst / hi_dst
+    int p2p_band(int ch, const size_t off[2], const Real* a, long long lo_src_row, long long hi_src_row, int rows, Real* dst, long long lo_dst_row,
+                 long long hi_dst_row) {
+        const unsigned long long seq = ++p2p_seq[ch];
+        const long long n16 = (long long)((size_t)rows * g.sy * sizeof(Real) / 16);
+        P2pPut pd{}; P2pGet gd{};
+        if (rank > 0) {
+            pd.src[0] = a + lo_src_row * g.sy; pd.dst[0] = peers.base[rank - 1] + off[1]; pd.flag[0] = &head_of(rank - 1)->flag[ch][1]; pd.n16[0] = n16;
+            gd.flag[0] = &head_of(rank)->flag[ch][0]; gd.src[0] = arena + off[0]; gd.dst[0] = dst ? dst + lo_dst_row * g.sy : nullptr; gd.n16[0] = n16;
+        }
+        if (rank + 1 < world) {
+            pd.src[1] = a + hi_src_row * g.sy; pd.dst[1] = peers.base[rank + 1] + off[0]; pd.flag[1] = &head_of(rank + 1)->flag[ch][0]; pd.n16[1] = n16;
+            gd.flag[1] = &head_of(rank)->flag[ch][1]; gd.src[1] = arena + off[1]; gd.dst[1] = dst ? dst + hi_dst_row * g.sy : nullptr; gd.n16[1] = n16;
+        }
+        const unsigned int nb = (unsigned int)std::min<long long>(kSMs, std::max<long long>(1, (n16 + 255) / 256));
+        LAUNCH(k_p2p_put, nb, 256, (const CgScal*)S, pd, seq, &head_of(rank)->ticket[ch]);
+        LAUNCH(k_p2p_wait_unpack, dst ? nb : 1u, 256, (const CgScal*)S, gd, seq);
+        CK(cudaGetLastError());
         return 0;
     }
 
@@ -824,6 +932,7 @@ struct Ctx final : CtxBase {
 
     // ---- multigrid hierarchy ------------------------------------------------------------------------
     int mg_setup() {
+        if (const char* e = getenv("INK_TRACE_ITER")) trace_iter = atoi(e);
         if (const char* e = getenv("INK_MG3_UNFUSED")) mg_fuse = (atoi(e) == 0);
         if (const char* e = getenv("INK_MG_TAIL_KB")) mg_tail_cap = (size_t)std::max(1, atoi(e)) * 1024;
         // measured (B200, 128x256x128): a tail holding only the coarsest (<= 1024-cell) level beats a deeper single-block tail
@@ -981,30 +1090,44 @@ struct Ctx final : CtxBase {
     // z = B r (result lv[0].xa, valid on own rows and `ovl` rows into each neighbour).  One GPU: one V-cycle.  Multi-GPU:
     // symmetric weighted overlapping Schwarz around the slab-local V-cycle — two band exchanges, no traffic inside the cycle.
     int precondition(Real* r) {
-        if (world == 1) return mg_vcycle(r);
+        if (world == 1) { const int rc = mg_vcycle(r); TR("vcycle"); return rc; }
         const long long sy = g.sy;
         const size_t brow = (size_t)ovl * sy;
-        if (int rc = halo_exchange(r, ovl, ovl)) return rc;
+        // r on the `ovl` rows beyond each interface: my bottom rows go to rank-1, my top rows to rank+1
+        if (p2p) { if (int rc = p2p_band(0, off_halo, r, g.j0, g.j1 - ovl, ovl, r, g.j0 - ovl, g.j1)) return rc; }
+        else if (int rc = halo_exchange(r, ovl, ovl)) return rc;
+        TR("r halo");
         struct Band { int ja, jb, peer; };
         Band bands[2] = {{g.j0 - ovl, g.j0 + ovl, rank - 1}, {g.j1 - ovl, g.j1 + ovl, rank + 1}};
         const bool has[2] = {rank > 0, rank + 1 < world};
         const unsigned int bb = (unsigned int)std::min<long long>(kMgBlocks, (2 * (long long)brow + 255) / 256);
         for (int b = 0; b < 2; ++b)
             if (has[b]) LAUNCH((k_band_scale<Real>), bb, 256, S, sy, bands[b].ja, bands[b].jb, g.j0, g.j1, d_sw, r, band_save[b]);
+        TR("band scale");
         if (int rc = mg_vcycle(r)) return rc;
+        TR("vcycle");
         Real* z = lv[0].xa;
         for (int b = 0; b < 2; ++b)
             if (has[b]) LAUNCH((k_band_restore_weight<Real>), bb, 256, S, sy, bands[b].ja, bands[b].jb, g.j0, g.j1, d_sw, r, band_save[b], z);
         CK(cudaGetLastError());
-        NK(nccl().GroupStart());
+        TR("band weight");
+        const Real* recv[2] = {band_recv[0], band_recv[1]};
+        if (p2p) {   // weighted z on both 2*ovl-row bands straight into the neighbours' arenas; combine reads it there
+            if (int rc = p2p_band(1, off_band, z, g.j0 - ovl, g.j1 - ovl, 2 * ovl, nullptr, 0, 0)) return rc;
+            recv[0] = reinterpret_cast<const Real*>(arena + off_band[0]);
+            recv[1] = reinterpret_cast<const Real*>(arena + off_band[1]);
+        } else {
+            NK(nccl().GroupStart());
+            for (int b = 0; b < 2; ++b)
+                if (has[b]) {
+                    NK(nccl().Send(z + (size_t)bands[b].ja * sy, 2 * brow, nc_real(), bands[b].peer, comm, stream));
+                    NK(nccl().Recv(band_recv[b], 2 * brow, nc_real(), bands[b].peer, comm, stream));
+                }
+            NK(nccl().GroupEnd());
+        }
         for (int b = 0; b < 2; ++b)
-            if (has[b]) {
-                NK(nccl().Send(z + (size_t)bands[b].ja * sy, 2 * brow, nc_real(), bands[b].peer, comm, stream));
-                NK(nccl().Recv(band_recv[b], 2 * brow, nc_real(), bands[b].peer, comm, stream));
-            }
-        NK(nccl().GroupEnd());
-        for (int b = 0; b < 2; ++b)
-            if (has[b]) LAUNCH((k_band_combine<Real>), bb, 256, S, sy, bands[b].ja, bands[b].jb, g.j0, g.j1, band_recv[b], r, z);
+            if (has[b]) LAUNCH((k_band_combine<Real>), bb, 256, S, sy, bands[b].ja, bands[b].jb, g.j0, g.j1, recv[b], r, z);
+        TR("z band combine");
         CK(cudaGetLastError());
         return 0;
     }
@@ -1026,8 +1149,7 @@ struct Ctx final : CtxBase {
         else LAUNCH((k_cg_init<Real, 1>), nb, 256, g, S, f, x, cg_r);
         CK(cudaGetLastError());
         if (dist) {
-            if (int rc = allreduce(S->loc, 4, ncclDouble, ncclSum)) return rc;
-            cg_post(0);
+            if (int rc = ar_post(0, 4, 0)) return rc;
         }
         const size_t head = offsetof(CgScal, partial);
         read_small(hS, S, head);
@@ -1043,8 +1165,7 @@ struct Ctx final : CtxBase {
             if (int rc = precondition(cg_r)) return rc;
             zsrc = lv[0].xa;
             if (dist) {
-                if (int rc = allreduce(S->loc + 2, 1, ncclDouble, ncclSum)) return rc;
-                cg_post(3);
+                if (int rc = ar_post(2, 1, 3)) return rc;
             }
         } else if (int rc = halo_exchange(zsrc, 1, 1)) return rc;
         // host polls convergence every `every` iterations; kernels launched after convergence are no-ops (S->done).
@@ -1054,12 +1175,15 @@ struct Ctx final : CtxBase {
             int batch = std::min(every, P.cg_max_iters - launched);
             if (use_mg && launched == 0 && prev_iters > 1) batch = std::min(prev_iters, P.cg_max_iters);
             for (int it = 0; it < batch; ++it) {
+                tracing = (trace_iter >= 0 && launched + it == trace_iter);
+                TR("start");
                 if (vec4()) LAUNCH((k_cg_dir_matvec<Real, 4>), nb, 256, g, S, zsrc, cg_d[dcur], cg_d[dcur ^ 1], cg_w, hlo, hhi);
                 else LAUNCH((k_cg_dir_matvec<Real, 1>), nb, 256, g, S, zsrc, cg_d[dcur], cg_d[dcur ^ 1], cg_w, hlo, hhi);
+                TR("matvec");
                 if (dist) {
-                    if (int rc = allreduce(S->loc, 1, ncclDouble, ncclSum)) return rc;
-                    cg_post(1);
+                    if (int rc = ar_post(0, 1, 1)) return rc;
                 }
+                TR("allreduce dw");
                 if (vec4()) {
                     if (use_mg) LAUNCH((k_cg_update<Real, 4, true>), nb, 256, g, S, x, cg_r, cg_d[dcur ^ 1], cg_w);
                     else LAUNCH((k_cg_update<Real, 4, false>), nb, 256, g, S, x, cg_r, cg_d[dcur ^ 1], cg_w);
@@ -1067,21 +1191,24 @@ struct Ctx final : CtxBase {
                     if (use_mg) LAUNCH((k_cg_update<Real, 1, true>), nb, 256, g, S, x, cg_r, cg_d[dcur ^ 1], cg_w);
                     else LAUNCH((k_cg_update<Real, 1, false>), nb, 256, g, S, x, cg_r, cg_d[dcur ^ 1], cg_w);
                 }
+                TR("update");
                 if (use_mg)
                     if (int rc = precondition(cg_r)) return rc;
                 if (dist) {
-                    if (int rc = allreduce(S->loc + 1, 2, ncclDouble, ncclSum)) return rc;
-                    cg_post(2);
+                    if (int rc = ar_post(1, 2, 2)) return rc;
+                    TR("allreduce rr,rz");
                     if (!use_mg)
                         if (int rc = halo_exchange(zsrc, 1, 1)) return rc;
                 }
                 dcur ^= 1;
+                tracing = false;
             }
             launched += batch;
             CK(cudaGetLastError());
             read_small(hS, S, head);
             CK(cudaStreamSynchronize(stream));
         }
+        tr_dump();
         prev_iters = hS->iters;
         stats.cg_iters = hS->iters;
         stats.cg_rel_residual = std::sqrt(hS->rr / hS->bb);
