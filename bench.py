@@ -379,6 +379,16 @@ def main():
     else:
         roof_p = None
 
+    # MAC stencil phases of the last timed step (CUDA events inside ink_step): algorithmic bytes per cell vs time.
+    # forces = K2b dilate + gravity (25 B/cell), viscosity = K3 (24), vorticity = K7a curl + K7b confinement (24 + 36; at N > 1 the
+    # phase also holds the velocity all-gather, so the fraction is only meaningful at N = 1)
+    mac_phases = {}
+    for name, bpc in (("forces", 25), ("viscosity", 24), ("vorticity", 60)):
+        ms = phase_acc.get(name, 0.0)
+        if ms > 0:
+            b = bpc * (rbytes / 4) * (ncell // world)
+            mac_phases[name] = {"ms": ms, "alg_bytes": b, "gbs": b / ms / 1e6, "frac": b / ms / 1e6 / peak}
+
     cpu = None
     if args.cpu_steps > 0 and world == 1:
         sample_n = min(n, args.cpu_particles)
@@ -401,7 +411,7 @@ def main():
         "particles_only_updates_per_s": n / (part_ms * 1e-3) if part_ms > 0 else None,
         "cg_iters_per_step": {"mean": float(np.mean(iters)), "min": int(min(iters)), "max": int(max(iters))},
         "phase_ms_last_step": phase_acc,
-        "roofline": roof, "pressure_phase": roof_p, "kernels": kernels, "cpu_baseline": cpu, "e2e": e2e,
+        "roofline": roof, "pressure_phase": roof_p, "mac_phases": mac_phases, "kernels": kernels, "cpu_baseline": cpu, "e2e": e2e,
         "gpu_launches": int(st1.kernel_launches - st0.kernel_launches) * world, "resorts_in_timed_region": int(st1.resorts - st0.resorts),
         "clocks": clocks,
     }

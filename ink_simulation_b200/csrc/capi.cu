@@ -21,6 +21,7 @@
 #include "mg_vec.cuh"
 #include "mg_tri.cuh"
 #include "p2p.cuh"
+#include "grid_vec.cuh"
 #include "nccl_shim.h"
 #include "particle_kernels.cuh"
 
@@ -122,6 +123,7 @@ struct Ctx final : CtxBase {
     Real* vel[2][3] = {{nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr}};
     int cur = 0;
     Real* curl[3] = {nullptr, nullptr, nullptr};
+    Real* curl_n = nullptr;   // |curl| per cell (vectorised K7a/K7b pair, grid_vec.cuh)
     Real *pres = nullptr, *q = nullptr, *rhs = nullptr, *cg_r = nullptr, *cg_d[2] = {nullptr, nullptr}, *cg_w = nullptr;
     bool have_q = false;
     // multigrid preconditioner (mg.cuh): lv[0..lt) run as global-memory kernels, the rest inside k_mg_tail
@@ -206,6 +208,7 @@ struct Ctx final : CtxBase {
         for (auto& b : vel)
             for (auto& p : b) cudaFree(p);
         for (auto& p : curl) cudaFree(p);
+        cudaFree(curl_n);
         cudaFree(pres); cudaFree(q); cudaFree(rhs); cudaFree(cg_r); cudaFree(cg_d[0]); cudaFree(cg_d[1]); cudaFree(cg_w);
         for (auto p : mg_alloc) cudaFree(p);
         cudaFree(d_sw);
@@ -274,6 +277,7 @@ struct Ctx final : CtxBase {
         for (auto& b : vel)
             for (auto& ptr : b) { CK(cudaMalloc(&ptr, nb)); CK(cudaMemsetAsync(ptr, 0, nb, stream)); }
         for (auto& ptr : curl) { CK(cudaMalloc(&ptr, nb)); CK(cudaMemsetAsync(ptr, 0, nb, stream)); }
+        CK(cudaMalloc(&curl_n, nb)); CK(cudaMemsetAsync(curl_n, 0, nb, stream));
         for (Real** ptr : {&pres, &q, &rhs, &cg_r, &cg_d[0], &cg_d[1], &cg_w}) { CK(cudaMalloc(ptr, nb)); CK(cudaMemsetAsync(*ptr, 0, nb, stream)); }
         CK(cudaMalloc(&S, sizeof(CgScal))); CK(cudaMemsetAsync(S, 0, sizeof(CgScal), stream));
         { const int dist = world > 1; CK(cudaMemcpyAsync(&S->dist, &dist, sizeof(int), cudaMemcpyHostToDevice, stream)); }
@@ -415,6 +419,8 @@ struct Ctx final : CtxBase {
     Real* Un(int a) { return vel[cur ^ 1][a]; }
     unsigned int cell_blocks() const { return nblk((long long)(g.j1 - g.j0) * g.sy); }
     static unsigned int cell_blocks(const Grid& q) { return nblk((long long)(q.j1 - q.j0) * q.sy); }
+    // vectorised stencil kernels (grid_vec.cuh): one thread per 4 z-consecutive cells
+    static unsigned int vec_blocks(const Grid& q) { return nblk((long long)(q.j1 - q.j0) * q.X * (q.Z / 4)); }
     // this rank's slab widened by `ext` rows each side (clipped to the grid): phases before a stencil phase are computed
     // redundantly on the rows the stencil will read, so the velocity phases need NO halo exchange (multi-GPU)
     Grid slab(int ext) const {
@@ -798,7 +804,8 @@ struct Ctx final : CtxBase {
     }
     int get_divergence(void* d, int hd) override {
         if (int rc = check_hd(hd, err)) return rc;
-        LAUNCH((k_divergence<Real>), cell_blocks(), 256, g, 0, Real(0), Real(0), U(0), U(1), U(2), rhs);
+        if (vec4()) LAUNCH((k_divergence_v4<Real>), vec_blocks(g), 256, g, 0, Real(0), Real(0), U(0), U(1), U(2), rhs);
+        else LAUNCH((k_divergence<Real>), cell_blocks(), 256, g, 0, Real(0), Real(0), U(0), U(1), U(2), rhs);
         CK(cudaGetLastError());
         if (int rc = allgather_rows(rhs, sizeof(Real))) return rc;
         return grid_out_any(rhs, d, hd);
@@ -909,7 +916,9 @@ struct Ctx final : CtxBase {
 
     int viscosity_impl(Real dt, int ext = 0) {
         const Real s = dt * C.visc;
-        { const Grid q = slab(ext); LAUNCH((k_viscosity<Real>), cell_blocks(q), 256, q, s, U(0), U(1), U(2), Un(0), Un(1), Un(2)); }
+        { const Grid q = slab(ext);
+          if (vec4()) LAUNCH((k_viscosity_v4<Real>), vec_blocks(q), 256, q, s, U(0), U(1), U(2), Un(0), Un(1), Un(2));
+          else LAUNCH((k_viscosity<Real>), cell_blocks(q), 256, q, s, U(0), U(1), U(2), Un(0), Un(1), Un(2)); }
         CK(cudaGetLastError());
         swap_vel();
         maxv_valid = false;
@@ -924,7 +933,8 @@ struct Ctx final : CtxBase {
         if (int rc = check_hd(hd, err)) return rc;
         const Real dt = (Real)(float)dt_;
         const Real scale = (C.rho * C.h) / dt;
-        LAUNCH((k_divergence<Real>), cell_blocks(), 256, g, 1, scale, C.patm, U(0), U(1), U(2), rhs);
+        if (vec4()) LAUNCH((k_divergence_v4<Real>), vec_blocks(g), 256, g, 1, scale, C.patm, U(0), U(1), U(2), rhs);
+        else LAUNCH((k_divergence<Real>), cell_blocks(), 256, g, 1, scale, C.patm, U(0), U(1), U(2), rhs);
         CK(cudaGetLastError());
         if (int rc = allgather_rows(rhs, sizeof(Real))) return rc;
         return grid_out_any(rhs, b, hd);
@@ -1217,7 +1227,9 @@ struct Ctx final : CtxBase {
 
     int grad_subtract(Real dt, int ext = 0) {
         const Real s = dt / (C.rho * C.h);
-        { const Grid q = slab(ext); LAUNCH((k_grad_subtract<Real>), cell_blocks(q), 256, q, s, pres, U(0), U(1), U(2)); }
+        { const Grid q = slab(ext);
+          if (vec4()) LAUNCH((k_grad_subtract_v4<Real>), vec_blocks(q), 256, q, s, pres, U(0), U(1), U(2));
+          else LAUNCH((k_grad_subtract<Real>), cell_blocks(q), 256, q, s, pres, U(0), U(1), U(2)); }
         CK(cudaGetLastError());
         maxv_valid = false;
         return 0;
@@ -1226,7 +1238,8 @@ struct Ctx final : CtxBase {
     // the pressure is exchanged ext + 1 rows down / ext rows up after the solve)
     int pressure_impl(Real dt, int ext = 0) {
         const Real scale = (C.rho * C.h) / dt;
-        LAUNCH((k_divergence<Real>), cell_blocks(), 256, g, 2, scale, C.patm, U(0), U(1), U(2), rhs);
+        if (vec4()) LAUNCH((k_divergence_v4<Real>), vec_blocks(g), 256, g, 2, scale, C.patm, U(0), U(1), U(2), rhs);
+        else LAUNCH((k_divergence<Real>), cell_blocks(), 256, g, 2, scale, C.patm, U(0), U(1), U(2), rhs);
         CK(cudaGetLastError());
         if (!(P.cg_warm_start && have_q)) CK(cudaMemsetAsync(q, 0, (size_t)g.n * sizeof(Real), stream));
         if (int rc = cg_solve(rhs, q)) return rc;
@@ -1258,9 +1271,12 @@ struct Ctx final : CtxBase {
     }
 
     int vorticity_impl(Real dt) {
-        { const Grid q = slab(1); LAUNCH((k_curl<Real>), cell_blocks(q), 256, q, U(0), U(1), U(2), curl[0], curl[1], curl[2]); }
+        { const Grid q = slab(1);
+          if (vec4()) LAUNCH((k_curl_v4<Real>), vec_blocks(q), 256, q, U(0), U(1), U(2), curl[0], curl[1], curl[2], curl_n);
+          else LAUNCH((k_curl<Real>), cell_blocks(q), 256, q, U(0), U(1), U(2), curl[0], curl[1], curl[2]); }
         CK(cudaMemsetAsync(d_scal, 0, sizeof(unsigned int), stream));
-        LAUNCH((k_vorticity<Real>), cell_blocks(), 256, g, dt, C.kvort, curl[0], curl[1], curl[2], U(0), U(1), U(2), d_scal);
+        if (vec4()) LAUNCH((k_vorticity_v4<Real>), vec_blocks(g), 256, g, dt, C.kvort, curl[0], curl[1], curl[2], curl_n, U(0), U(1), U(2), d_scal);
+        else LAUNCH((k_vorticity<Real>), cell_blocks(), 256, g, dt, C.kvort, curl[0], curl[1], curl[2], U(0), U(1), U(2), d_scal);
         CK(cudaGetLastError());
         if (int rc = allreduce(d_scal, 1, ncclUint32, ncclMax)) return rc;
         maxv_valid = true;   // fused K0
