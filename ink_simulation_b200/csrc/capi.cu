@@ -135,6 +135,8 @@ struct Ctx final : CtxBase {
     bool use_mg = false;
     bool mg_fuse = true;    // INK_MG3_UNFUSED=1 (debug / A-B): separate residual and full 4x4x4 restriction kernels
     size_t mg_tail_cap = 200 * 1024;   // INK_MG_TAIL_KB: shared-memory budget of the single-block tail (experiments)
+    int mg_lc = -1;           // >= 1: levels [mg_lc, mg_lt] run in ONE persistent launch (k_mg3_coarse); -1: per-level kernels
+    unsigned int* mg_bar = nullptr;
     bool mg_tri = false;   // trilinear V(1,1) (mg_tri.cuh) instead of piecewise-constant V(2,2) (mg.cuh)
     int prev_iters = 0;
     // multi-GPU: overlapping-Schwarz extension of the slab the V-cycle runs on (mg_vec.cuh)
@@ -211,6 +213,7 @@ struct Ctx final : CtxBase {
         cudaFree(curl_n);
         cudaFree(pres); cudaFree(q); cudaFree(rhs); cudaFree(cg_r); cudaFree(cg_d[0]); cudaFree(cg_d[1]); cudaFree(cg_w);
         for (auto p : mg_alloc) cudaFree(p);
+        cudaFree(mg_bar);
         cudaFree(d_sw);
         for (auto p : band_save) cudaFree(p);
         for (auto p : band_recv) cudaFree(p);
@@ -1014,6 +1017,21 @@ struct Ctx final : CtxBase {
         }
         CK(cudaFuncSetAttribute(k_mg_tail<Real>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mg_tail_smem));
         CK(cudaFuncSetAttribute(k_mg3_tail<Real>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mg_tail_smem));
+        // Persistent coarse-level kernel: OFF by default.  Measured on B200 (128x256x128): 63 us for levels 2..4 in one launch
+        // (7 device-side grid barriers, 32 blocks) against ~40 us for the same levels as 10 PDL-chained launches that use the
+        // whole GPU; step 2.35 vs 1.97 ms.  Kept opt-in (INK_MG_COARSE=1) as the starting point for a cluster/DSMEM version.
+        if (mg_tri && getenv("INK_MG_COARSE") && atoi(getenv("INK_MG_COARSE")) != 0) {
+            for (int l = 1; l < mg_lt; ++l) {
+                const MgDims& d = lv[l].d;
+                if ((long long)d.X * (d.j1 - d.j0) * d.Z <= kMg3CoarseCells) { mg_lc = l; break; }
+            }
+            if (mg_lc >= 1 && mg_lt - mg_lc + 1 > kMg3CoarseMaxLevels) mg_lc = -1;
+            if (mg_lc >= 1) {
+                CK(cudaMalloc(&mg_bar, 2 * sizeof(unsigned int)));
+                CK(cudaMemsetAsync(mg_bar, 0, 2 * sizeof(unsigned int), stream));
+                CK(cudaFuncSetAttribute(k_mg3_coarse<Real>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mg_tail_smem));
+            }
+        }
         use_mg = true;
         return 0;
     }
@@ -1026,7 +1044,8 @@ struct Ctx final : CtxBase {
         auto rhs = [&](int l) -> const Real* { return l == 0 ? r0 : lv[l].r; };
         if (mg_tri) {
             // V(1,1), trilinear transfer: 3 launches per global level (residual, restrict | up), xb = residual scratch
-            for (int l = 0; l < mg_lt; ++l) {
+            const int l_split = mg_lc >= 1 ? mg_lc : mg_lt;   // levels below l_split: one kernel per pass
+            for (int l = 0; l < l_split; ++l) {
                 const MgDims &df = lv[l].d, &dc = lv[l + 1].d;
                 if (df.Z % 4 == 0 && mg_fuse) {   // residual + z-restriction fused (xb holds the half-size z-restricted residual)
                     const long long nv = (long long)df.X * (df.j1 - df.j0) * (df.Z / 4);
@@ -1035,6 +1054,7 @@ struct Ctx final : CtxBase {
                         const long long nc4 = (long long)dc.X * (dc.j1 - dc.j0) * (dc.Z / 4);
                         LAUNCH((k_mg3_restrict_xy_v4<Real>), (unsigned int)std::min<long long>(kMgBlocks, std::max<long long>(1, (nc4 + 255) / 256)), 256, S, df, dc, lv[l].xb, lv[l + 1].r);
                     } else LAUNCH((k_mg3_restrict_xy<Real>), mg_blocks(dc), 256, S, df, dc, lv[l].xb, lv[l + 1].r);
+                    TR(l == 0 ? "down L0" : l == 1 ? "down L1" : "down L2+");
                     continue;
                 }
                 if (df.Z % 4 == 0) {
@@ -1043,13 +1063,24 @@ struct Ctx final : CtxBase {
                 } else LAUNCH((k_mg3_residual<Real>), mg_blocks(df), 256, S, df, rhs(l), lv[l].xb);
                 LAUNCH((k_mg3_restrict<Real>), mg_blocks(dc), 256, S, df, dc, lv[l].xb, lv[l + 1].r);
             }
-            {
+            if (mg_lc >= 1) {   // levels mg_lc .. mg_lt (down, tail, up) in one persistent launch
+                Mg3CoarseArgs<Real> A{};
+                A.nlev = mg_lt - mg_lc + 1;
+                for (int q = 0; q < A.nlev; ++q) A.lv[q] = lv[mg_lc + q];
+                A.tail = mg_tail;
+                A.tail_off = (long long)lv[mg_lt].d.j0 * lv[mg_lt].d.X * lv[mg_lt].d.Z;
+                A.bar = mg_bar;
+                launch_k(k_mg3_coarse<Real>, kMg3CoarseBlocks, kMg3CoarseThreads, mg_tail_smem, stream, S, A);
+                ++stats.kernel_launches;
+                TR("coarse levels");
+            } else {
                 const MgDims& d = lv[mg_lt].d;
                 const long long off = (long long)d.j0 * d.X * d.Z;
                 launch_k(k_mg3_tail<Real>, 1, kMgTailThreads, mg_tail_smem, stream, S, mg_tail, rhs(mg_lt) + off, lv[mg_lt].xa + off);
                 ++stats.kernel_launches;
+                TR("tail");
             }
-            for (int l = mg_lt - 1; l >= 0; --l) {
+            for (int l = l_split - 1; l >= 0; --l) {
                 const MgDims &df = lv[l].d, &dc = lv[l + 1].d;
                 // one coarse cell per thread, no grid-stride tail (a thread's work is ~700 instructions); the fp64 partials of
                 // block_sum_last cap the FINAL launch at kCgMaxBlocks blocks
@@ -1057,6 +1088,7 @@ struct Ctx final : CtxBase {
                 const unsigned int ub = (unsigned int)std::max<long long>(1, (ncc + 255) / 256);
                 if (l == 0) LAUNCH((k_mg3_up<Real, true>), std::min<unsigned int>(ub, kCgMaxBlocks), 256, S, df, dc, lv[l].s, rhs(l), lv[l + 1].xa, lv[l].xa, dot0, dot1);
                 else LAUNCH((k_mg3_up<Real, false>), ub, 256, S, df, dc, lv[l].s, rhs(l), lv[l + 1].xa, lv[l].xa, 0, 0);
+                TR(l == 0 ? "up L0" : l == 1 ? "up L1" : "up L2+");
             }
             CK(cudaGetLastError());
             return 0;

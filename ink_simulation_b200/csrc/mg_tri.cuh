@@ -334,15 +334,14 @@ __device__ __forceinline__ Real mg3_res_at(const MgDims& d, const Real* __restri
     const Real rc = r[c];
     return rc - (Real(kMgOmega) / Real(6)) * (Real(6) * rc - mg_nbr_sum(d, r, i, j, k, c));
 }
+// gtid / gnth: global thread id and thread count of the (possibly multi-block) team; gnth must be a multiple of 32
 template <class Real>
-__global__ void __launch_bounds__(256) k_mg3_residual_rz_v4(const CgScal* S, MgDims d, const Real* __restrict__ r, Real* __restrict__ resz) {
-    INK_PDL();
-    if (S->done) return;
+__device__ __forceinline__ void mg3_residual_rz_v4_dev(const MgDims& d, const Real* __restrict__ r, Real* __restrict__ resz, unsigned int gtid, unsigned int gnth) {
     const Real w6 = Real(kMgOmega) / Real(6);
     const unsigned int ZV = (unsigned int)d.Z >> 2;
     const unsigned int tot = (unsigned int)(d.j1 - d.j0) * (unsigned int)d.X * ZV;
     const unsigned int lane = threadIdx.x & 31u;
-    for (unsigned int base = blockIdx.x * blockDim.x + threadIdx.x - lane; base < tot; base += gridDim.x * blockDim.x) {   // warp-uniform trip count
+    for (unsigned int base = gtid - lane; base < tot; base += gnth) {   // warp-uniform trip count
         int i = 0, j = 0, k = 0; long long c = 0;
         Real res[4] = {Real(0), Real(0), Real(0), Real(0)};
         const bool act = mg_vec_cell(d, base + lane, i, j, k, c);
@@ -366,6 +365,12 @@ __global__ void __launch_bounds__(256) k_mg3_residual_rz_v4(const CgScal* S, MgD
             stp<Real, 2>(resz + (c >> 1), o);   // c = row * Z + k, Z and k even: (row * Z/2 + k/2)
         }
     }
+}
+template <class Real>
+__global__ void __launch_bounds__(256) k_mg3_residual_rz_v4(const CgScal* S, MgDims d, const Real* __restrict__ r, Real* __restrict__ resz) {
+    INK_PDL();
+    if (S->done) return;
+    mg3_residual_rz_v4_dev<Real>(d, r, resz, blockIdx.x * blockDim.x + threadIdx.x, gridDim.x * blockDim.x);
 }
 // rc[I,J,K] = sum over the 4x4 fine columns (2I-1..2I+2, 2J-1..2J+2) of wx wy resz[.,.,K]
 template <class Real>
@@ -396,11 +401,10 @@ __global__ void __launch_bounds__(256) k_mg3_restrict_xy(const CgScal* S, MgDims
 // same, coarse Z % 4 == 0: one thread per 4 z-consecutive coarse cells, 16 LDG.128 + 1 STG.128 (the scalar kernel is
 // issue-bound on index arithmetic and validity tests: 62 % issue slots at 7 % of DRAM peak, profiles/r1_c_mg3_down.txt)
 template <class Real>
-__global__ void __launch_bounds__(256) k_mg3_restrict_xy_v4(const CgScal* S, MgDims df, MgDims dc, const Real* __restrict__ resz, Real* __restrict__ rc) {
-    INK_PDL();
-    if (S->done) return;
+__device__ __forceinline__ void mg3_restrict_xy_v4_dev(const MgDims& df, const MgDims& dc, const Real* __restrict__ resz, Real* __restrict__ rc, unsigned int gtid,
+                                                       unsigned int gnth) {
     int i, j, k; long long c;
-    for (unsigned int t = blockIdx.x * blockDim.x + threadIdx.x; mg_vec_cell(dc, t, i, j, k, c); t += gridDim.x * blockDim.x) {
+    for (unsigned int t = gtid; mg_vec_cell(dc, t, i, j, k, c); t += gnth) {
         Real acc[4] = {Real(0), Real(0), Real(0), Real(0)};
 #pragma unroll
         for (int n = 0; n < 4; ++n) {
@@ -423,12 +427,16 @@ __global__ void __launch_bounds__(256) k_mg3_restrict_xy_v4(const CgScal* S, MgD
         stp<Real, 4>(rc + c, o);
     }
 }
+template <class Real>
+__global__ void __launch_bounds__(256) k_mg3_restrict_xy_v4(const CgScal* S, MgDims df, MgDims dc, const Real* __restrict__ resz, Real* __restrict__ rc) {
+    INK_PDL();
+    if (S->done) return;
+    mg3_restrict_xy_v4_dev<Real>(df, dc, resz, rc, blockIdx.x * blockDim.x + threadIdx.x, gridDim.x * blockDim.x);
+}
 
 // ---- shared-memory tail: all levels from `lt` down in ONE block (MgTailArgs of mg.cuh; 3 arrays per level) ----------
 template <class Real>
-__global__ void __launch_bounds__(kMgTailThreads) k_mg3_tail(CgScal* S, MgTailArgs A, const Real* __restrict__ rin, Real* __restrict__ xout) {
-    INK_PDL();
-    if (S->done) return;
+__device__ __forceinline__ void mg3_tail_dev(CgScal* S, const MgTailArgs& A, const Real* __restrict__ rin, Real* __restrict__ xout) {
     extern __shared__ __align__(16) unsigned char mg_smem_raw[];
     Real* sm = reinterpret_cast<Real*>(mg_smem_raw);
     const long long tid = threadIdx.x, nth = blockDim.x;
@@ -495,6 +503,89 @@ __global__ void __launch_bounds__(kMgTailThreads) k_mg3_tail(CgScal* S, MgTailAr
             if (S->dist) S->loc[2] = t; else { S->rz_old = S->rz; S->rz = t; }
         }
     }
+}
+template <class Real>
+__global__ void __launch_bounds__(kMgTailThreads) k_mg3_tail(CgScal* S, MgTailArgs A, const Real* __restrict__ rin, Real* __restrict__ xout) {
+    INK_PDL();
+    if (S->done) return;
+    mg3_tail_dev<Real>(S, A, rin, xout);
+}
+
+// ---- persistent coarse-level kernel: every level below kMg3CoarseCells cells in ONE launch ----------------------------------
+// Levels with <= ~100 k cells are launch-latency bound: each of their 3 kernels costs 4-5 us for < 1 us of work, ~55 us of
+// a ~120 us PCG iteration at 128x256x128 (INK_TRACE_ITER timeline, profiles/r1_e_trace.txt).  Here a small co-resident team
+// of blocks walks down and up those levels with a device-side grid barrier between passes (arrays stay in global memory =
+// L2; block 0 runs the shared-memory tail).  Safe with plain/non-coherent loads: inside one launch every array element is
+// written in exactly one pass and only read in later passes, so no SM can hold a stale L1 line for it.
+constexpr int kMg3CoarseCells = 131072;
+constexpr int kMg3CoarseBlocks = 32;
+constexpr int kMg3CoarseThreads = 512;
+constexpr int kMg3CoarseMaxLevels = 6;
+
+__device__ __forceinline__ void mg_grid_barrier(unsigned int* bar) {   // bar[0] = arrivals, bar[1] = generation
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        volatile unsigned int* gen = bar + 1;
+        __threadfence();
+        const unsigned int g = *gen;
+        if (atomicAdd(bar, 1u) == gridDim.x - 1) {
+            bar[0] = 0;
+            __threadfence();
+            *gen = g + 1;
+        } else {
+            while (*gen == g) { }
+        }
+        __threadfence();
+    }
+    __syncthreads();
+}
+
+template <class Real>
+struct Mg3CoarseArgs {
+    int nlev;                                  // levels handled here; the last one is the top of the shared-memory tail
+    MgLevelPtrs<Real> lv[kMg3CoarseMaxLevels];
+    MgTailArgs tail;
+    long long tail_off;                        // element offset of the tail's slab in its level arrays
+    unsigned int* bar;
+};
+
+template <class Real>
+__global__ void __launch_bounds__(kMg3CoarseThreads) k_mg3_coarse(CgScal* S, Mg3CoarseArgs<Real> A) {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (S->done) return;                       // uniform: nobody writes `done` during this launch
+    const unsigned int gtid = blockIdx.x * blockDim.x + threadIdx.x, gnth = gridDim.x * blockDim.x;
+    for (int q = 0; q + 1 < A.nlev; ++q) {     // down
+        const MgDims &df = A.lv[q].d, &dc = A.lv[q + 1].d;
+        if (df.Z % 4 == 0) mg3_residual_rz_v4_dev<Real>(df, A.lv[q].r, A.lv[q].xb, gtid, gnth);
+        else mg3_residual<Real>(df, A.lv[q].r, A.lv[q].xb, gtid, gnth);
+        mg_grid_barrier(A.bar);
+        if (df.Z % 4 == 0 && dc.Z % 4 == 0) mg3_restrict_xy_v4_dev<Real>(df, dc, A.lv[q].xb, A.lv[q + 1].r, gtid, gnth);
+        else if (df.Z % 4 == 0) {              // z-restricted residual, scalar x-y gather
+            INK_MG_CELL_LOOP(dc, gtid, gnth) {
+                INK_MG_DECODE(dc)
+                Real acc = Real(0);
+                for (int n = 0; n < 4; ++n) {
+                    const int fj = 2 * j - 1 + n;
+                    if (fj < df.j0 || fj >= df.j1) continue;
+                    const Real wy = (n == 1 || n == 2) ? Real(0.75) : Real(0.25);
+                    for (int l = 0; l < 4; ++l) {
+                        const int fi = 2 * i - 1 + l;
+                        if (fi < 0 || fi >= df.X) continue;
+                        acc += wy * ((l == 1 || l == 2) ? Real(0.75) : Real(0.25)) * A.lv[q].xb[((long long)fj * df.X + fi) * dc.Z + k];
+                    }
+                }
+                A.lv[q + 1].r[c] = acc;
+            }
+        } else mg3_restrict<Real>(df, dc, A.lv[q].xb, A.lv[q + 1].r, gtid, gnth);
+        mg_grid_barrier(A.bar);
+    }
+    if (blockIdx.x == 0) mg3_tail_dev<Real>(S, A.tail, A.lv[A.nlev - 1].r + A.tail_off, A.lv[A.nlev - 1].xa + A.tail_off);
+    mg_grid_barrier(A.bar);
+    for (int q = A.nlev - 2; q >= 0; --q) {    // up
+        mg3_up<Real>(A.lv[q].d, A.lv[q + 1].d, A.lv[q].s, A.lv[q].r, A.lv[q + 1].xa, A.lv[q].xa, gtid, gnth);
+        if (q > 0) mg_grid_barrier(A.bar);
+    }
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 }
 #endif  // __CUDACC__
 
