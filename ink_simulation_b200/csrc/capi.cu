@@ -9,6 +9,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
+#include <chrono>
 #include <cstring>
 #include <string>
 #include <utility>
@@ -150,7 +151,7 @@ struct Ctx final : CtxBase {
     // multi-GPU: per-iteration exchanges by peer stores over NVLink (p2p.cuh) instead of NCCL calls
     bool p2p = false;
     // INK_TRACE_ITER=k: CUDA-event timeline of CG iteration k of every solve, printed by rank 0 (diagnostic)
-    int trace_iter = -1; bool tracing = false;
+    int trace_iter = -1; bool tracing = false; bool host_timing = false;
     std::vector<cudaEvent_t> tr_ev; std::vector<const char*> tr_name;
     void TR(const char* name) {
         if (!tracing) return;
@@ -946,6 +947,7 @@ struct Ctx final : CtxBase {
     // ---- multigrid hierarchy ------------------------------------------------------------------------
     int mg_setup() {
         if (const char* e = getenv("INK_TRACE_ITER")) trace_iter = atoi(e);
+        if (const char* e = getenv("INK_HOSTTIME")) host_timing = atoi(e) != 0;
         if (const char* e = getenv("INK_MG3_UNFUSED")) mg_fuse = (atoi(e) == 0);
         if (const char* e = getenv("INK_MG_TAIL_KB")) mg_tail_cap = (size_t)std::max(1, atoi(e)) * 1024;
         // measured (B200, 128x256x128): a tail holding only the coarsest (<= 1024-cell) level beats a deeper single-block tail
@@ -1215,6 +1217,7 @@ struct Ctx final : CtxBase {
         const int every = use_mg ? 2 : std::max(1, P.cg_check_every);
         while (!hS->done && launched < P.cg_max_iters) {
             int batch = std::min(every, P.cg_max_iters - launched);
+            const auto t_batch = std::chrono::steady_clock::now();
             if (use_mg && launched == 0 && prev_iters > 1) batch = std::min(prev_iters, P.cg_max_iters);
             for (int it = 0; it < batch; ++it) {
                 tracing = (trace_iter >= 0 && launched + it == trace_iter);
@@ -1248,7 +1251,13 @@ struct Ctx final : CtxBase {
             launched += batch;
             CK(cudaGetLastError());
             read_small(hS, S, head);
+            const auto t_enq = std::chrono::steady_clock::now();
             CK(cudaStreamSynchronize(stream));
+            if (host_timing && rank == 0) {   // INK_HOSTTIME=1: is the host (launch rate) or the device the bottleneck of the solve?
+                const auto t_done = std::chrono::steady_clock::now();
+                fprintf(stderr, "[inkb200 host] CG batch of %d iterations: enqueue %.0f us, then blocked %.0f us waiting for the device\n", batch,
+                        std::chrono::duration<double, std::micro>(t_enq - t_batch).count(), std::chrono::duration<double, std::micro>(t_done - t_enq).count());
+            }
         }
         tr_dump();
         prev_iters = hS->iters;
