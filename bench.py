@@ -29,6 +29,9 @@ CONFIGS = {
     "c2": dict(dims=(20, 45, 20), particles=100_000, cloud="box"),
     "c3": dict(dims=(128, 256, 128), particles=10_000_000, cloud="uniform"),
     "c4": dict(dims=(256, 256, 256), particles=100_000_000, cloud="uniform"),
+    # BASELINE config 5: RK2 advection sweep on a FROZEN 512^3 analytic field, 125 M particles per GPU (1 B at 8 GPUs); every
+    # rank holds the whole field (broadcast once, no per-step traffic), particles shard by index
+    "c5": dict(dims=(512, 512, 512), particles=125_000_000, cloud="uniform", sweep=True),
 }
 RENDER_DT = 0.35  # src/main.cpp:25
 
@@ -123,10 +126,17 @@ def cpu_port_sample(dims, pos, steps, warm_state=None):
 
 def workload_config(args, cfg, dims, n, world):
     """The `config` object both arms print (the reference arm runs a bounded sample of it and says which)."""
+    if cfg.get("sweep"):
+        X, Y, Z = cfg["dims"]
+        per = args.particles or cfg["particles"]
+        return {"workload": f"{args.config}: RK2 advection sweep (System::updateParticles), {per * world} particles ({per} per GPU, uniform, unsorted "
+                            f"input), frozen analytic {X}x{Y}x{Z} field replicated on every GPU, dt = 0.2", "arith": args.arith,
+                "resort_interval": args.resort, "sharding": "particles by index, no data-path collective",
+                "l2": "field 1.6 GB + particle arrays 4.5 GB per pass >> L2 (126 MB)"}
     return {"workload": f"{args.config}: {n} particles ({cfg['cloud']}, unsorted input), {dims[0]}x{dims[1]}x{dims[2]} MAC grid, "
                         f"full System::solve per step", "arith": args.arith, "cg_rtol": args.cg_rtol,
             "resort_interval": args.resort, "precond": args.precond,
-            "sharding": "single GPU" if world == 1 else f"{world} y-slabs of {dims[1] // world} rows, particles by index; NCCL",
+            "sharding": "single GPU" if world == 1 else f"{world} y-slabs of {dims[1] // world} rows, particles by index; NCCL + peer-memory exchanges",
             "l2": "inputs larger than L2 (per GPU: particle arrays 360 MB + 15 grid vectors of 16.8 MB; L2 = 126 MB)"}
 
 
@@ -149,14 +159,26 @@ def run_reference_arm(args, cfg, rank, world):
         T = oracle.OracleSystem(*dims, dtype=np.float32)
         kind, cores = "port", os.cpu_count()
     T.set_particles(pos)
+    if cfg.get("sweep"):   # config 5: particles-only sweep on the frozen analytic field (same field as run_sweep)
+        X, Y, Z = dims
+        ax = [np.arange(m, dtype=np.float32) * np.float32(2 * np.pi / m) for m in dims]
+        gx, gy, gz = ax[0][:, None, None], ax[1][None, :, None], ax[2][None, None, :]
+        u = np.broadcast_to(np.sin(gz) + np.cos(gy), dims).astype(np.float32)
+        v = np.broadcast_to(np.sin(gx) + np.cos(gz), dims).astype(np.float32)
+        w = np.broadcast_to(np.sin(gy) + np.cos(gx), dims).astype(np.float32)
+        mx = np.float32(np.sqrt(u * u + v * v + w * w).max())
+        T.set_velocity(u / mx, v / mx, w / mx)
+        step = lambda: T.particles(0.2)
+    else:
+        step = lambda: T.solve(RENDER_DT)
     for _ in range(args.warmup):
-        T.solve(RENDER_DT)
+        step()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        T.solve(RENDER_DT)
+        step()
     sec = (time.perf_counter() - t0) / args.steps
     val = sample_n / sec
-    sample = (f"{args.steps} System::solve steps of one GPU's share of the workload: grid {dims[0]}x{dims[1]}x{dims[2]}, {sample_n} particles "
+    sample = (f"{args.steps} {'updateParticles sweeps' if cfg.get('sweep') else 'System::solve steps'} of one GPU's share of the workload: grid {dims[0]}x{dims[1]}x{dims[2]}, {sample_n} particles "
               f"({cfg['cloud']}); {'compiled reference, 1 thread (it has no threading)' if use_ref else 'OpenMP oracle port, exact DST Poisson solve'}")
     wdims, wn = dims, n
     if world > 1 and not args.strong:
@@ -171,6 +193,76 @@ def run_reference_arm(args, cfg, rank, world):
         "e2e": {"value": val, "unit": "particle-updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
+
+
+def run_sweep(args, cfg, rank, world, local):
+    """Config 5: particles-only RK2 sweep (ink_particles = System::updateParticles) on a frozen analytic field.  Every rank is a
+    single-GPU System holding the WHOLE field and its index shard of the particles: no data-path collective (weak scaling)."""
+    import torch
+
+    from ink_simulation_b200 import System
+
+    dims, n_local = cfg["dims"], args.particles or cfg["particles"]
+    X, Y, Z = dims
+    ncell = X * Y * Z
+    S = System(*dims, dtype=np.float32, arith=args.arith, device=local, resort_interval=args.resort)
+    # ABC-type flow, max |u| = 1  =>  dt = K_CFL * h / maxV = 0.2 (SURVEY 8d); built on the device, (X, Y, Z) C-order
+    dev = torch.device("cuda", local)
+    ax = [torch.arange(m, device=dev, dtype=torch.float32) * (2 * np.pi / m) for m in dims]
+    gx, gy, gz = ax[0][:, None, None], ax[1][None, :, None], ax[2][None, None, :]
+    u = (torch.sin(gz) + torch.cos(gy)).expand(X, Y, Z).contiguous()
+    v = (torch.sin(gx) + torch.cos(gz)).expand(X, Y, Z).contiguous()
+    w = (torch.sin(gy) + torch.cos(gx)).expand(X, Y, Z).contiguous()
+    mx = float(torch.sqrt(u * u + v * v + w * w).max())
+    for f in (u, v, w):
+        f.div_(mx)
+    S.set_velocity(u, v, w)
+    del u, v, w, gx, gy, gz
+    torch.cuda.empty_cache()
+    pos = torch.from_numpy(make_particles(dims, n_local * world, "uniform", first=rank * n_local, count=n_local))
+    S.set_particles_shard(pos)
+    del pos
+    dt = 0.2
+    for _ in range(max(3, args.warmup)):
+        S.particles(dt)
+    torch.cuda.synchronize()
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier(); torch.cuda.synchronize()
+    st0 = S.stats()
+    sampler = ClockSampler(local)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        S.particles(dt)
+    S.sync()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    clocks = sampler.stop()
+    st1 = S.stats()
+    ms_step = ms / args.steps
+    peak, peak_src = peaks()
+    alg = 36 * n_local + 12 * ncell
+    gbs = alg / ms_step / 1e6
+    line = {
+        "metric": "particle_rk2_updates_per_s", "value": n_local * world / (ms_step * 1e-3), "unit": "particle-updates/s", "n_gpus": world,
+        "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, cfg, dims, n_local * world, world),
+        "roofline": {"kernel": f"k_particles_rk2<f32,{args.arith}> (+ periodic re-binning inside the timed region)", "bound": "hbm",
+                     "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak, "traffic": None, "alg_bytes_per_launch": alg,
+                     "peak_source": peak_src},
+        "cpu_baseline": None, "e2e": None,
+        "gpu_launches": int(st1.kernel_launches - st0.kernel_launches) * world, "resorts_in_timed_region": int(st1.resorts - st0.resorts),
+        "clocks": clocks,
+    }
+    if rank == 0:
+        print(json.dumps(line), flush=True)
 
 
 def main():
@@ -218,6 +310,11 @@ def main():
     if world > 1 and not args.strong:   # weak scaling: every GPU keeps one config-sized y-slab and particle shard
         dims = (dims[0], dims[1] * world, dims[2])
         n = n * world
+    if cfg.get("sweep"):
+        run_sweep(args, cfg, rank, world, local)
+        if world > 1:
+            dist.destroy_process_group()
+        return
     ncell = dims[0] * dims[1] * dims[2]
     dtype = np.float32 if args.dtype == "f32" else np.float64
     rbytes = 4 if args.dtype == "f32" else 8
@@ -401,7 +498,7 @@ def main():
 
     water_ms = sum(phase_acc.get(k, 0.0) for k in ("dt", "advect", "forces", "viscosity", "pressure", "vorticity"))
     line = {
-        "metric": "particle_rk2_updates_per_s", "value": value, "unit": "particle-updates/s", "n_gpus": 1, "steps": args.steps,
+        "metric": "particle_rk2_updates_per_s", "value": value, "unit": "particle-updates/s", "n_gpus": world, "steps": args.steps,
         "warmup": max(3, args.warmup), "ms_per_step": ms_step, "higher_is_better": True,
         "scaling": "strong" if (world > 1 and args.strong) else "weak", "vs_baseline": None,
         "dtype": args.dtype, "data": "synthetic",
