@@ -211,6 +211,11 @@ class System:
         return pos, vel
 
     def set_velocity(self, u, v, w):
+        if hasattr(u, "data_ptr"):   # torch tensors (host or DEVICE), contiguous, (X, Y, Z): pointers go straight to the C ABI
+            assert tuple(u.shape) == self.dims and tuple(v.shape) == self.dims and tuple(w.shape) == self.dims
+            assert u.is_contiguous() and v.is_contiguous() and w.is_contiguous()
+            self._ck(self.L.ink_set_velocity(self.h, _ptr(u), _ptr(v), _ptr(w), 32 if u.element_size() == 4 else 64))
+            return
         u, v, w = self._a(u), self._a(v), self._a(w)
         assert u.shape == self.dims and v.shape == self.dims and w.shape == self.dims
         self._ck(self.L.ink_set_velocity(self.h, _ptr(u), _ptr(v), _ptr(w), self.hd))
