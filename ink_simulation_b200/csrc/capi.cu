@@ -171,7 +171,8 @@ struct Ctx final : CtxBase {
     unsigned char* arena = nullptr;
     P2pPeers peers{};
     size_t off_halo[2] = {0, 0}, off_band[2] = {0, 0};   // payload regions: [0] written by rank-1, [1] by rank+1
-    unsigned long long p2p_seq[2] = {0, 0};              // host sequence numbers of channel 0 (r halo) and 1 (z band)
+    unsigned long long p2p_seq[2] = {0, 0};
+    unsigned long long r_seq = 0;   // sequence number under which the producer of the current residual pushed its boundary rows              // host sequence numbers of channel 0 (r halo) and 1 (z band)
     uint8_t *seed = nullptr, *mark = nullptr;
     unsigned int* d_scal = nullptr;  // [0] max speed bits, [1] oob particle count
     unsigned int* h_scal = nullptr;  // pinned
@@ -391,6 +392,19 @@ struct Ctx final : CtxBase {
         LAUNCH(k_p2p_wait_unpack, dst ? nb : 1u, 256, (const CgScal*)S, gd, seq);
         CK(cudaGetLastError());
         return 0;
+    }
+
+    // boundary rows of the residual about to be produced (k_cg_init / k_cg_update) go straight into the neighbours' arenas
+    P2pPush make_push() {
+        P2pPush p{};
+        if (!(p2p && use_mg)) return p;
+        p.on = 1;
+        p.seq = r_seq = ++p2p_seq[0];
+        p.lo_cells = (long long)ovl * g.sy;
+        p.hi_start = (long long)(g.j1 - g.j0 - ovl) * g.sy;
+        if (rank > 0) { p.dst_lo = peers.base[rank - 1] + off_halo[1]; p.flag_lo = &head_of(rank - 1)->flag[0][1]; }
+        if (rank + 1 < world) { p.dst_hi = peers.base[rank + 1] + off_halo[0]; p.flag_hi = &head_of(rank + 1)->flag[0][0]; }
+        return p;
     }
 
     // ---- helpers ---------------------------------------------------------------------------------
@@ -952,7 +966,7 @@ struct Ctx final : CtxBase {
         if (const char* e = getenv("INK_MG_TAIL_KB")) mg_tail_cap = (size_t)std::max(1, atoi(e)) * 1024;
         // measured (B200, 128x256x128): a tail holding only the coarsest (<= 1024-cell) level beats a deeper single-block tail
         // (2.59 vs 2.73 ms/step): one block of 1024 threads is issue-bound on the 8192-cell level
-        if (mg_tri && !getenv("INK_MG_TAIL_KB")) mg_tail_cap = 16 * 1024;
+        if (mg_tri && !getenv("INK_MG_TAIL_KB")) mg_tail_cap = 32 * 1024;
         const size_t smem_cap = std::min<size_t>(mg_tail_cap, 200 * 1024);
         std::vector<MgDims> abs_d;
         je0 = g.j0; je1 = g.j1; dot0 = g.j0; dot1 = g.j1;
@@ -1138,26 +1152,42 @@ struct Ctx final : CtxBase {
         const long long sy = g.sy;
         const size_t brow = (size_t)ovl * sy;
         // r on the `ovl` rows beyond each interface: my bottom rows go to rank-1, my top rows to rank+1
-        if (p2p) { if (int rc = p2p_band(0, off_halo, r, g.j0, g.j1 - ovl, ovl, r, g.j0 - ovl, g.j1)) return rc; }
-        else if (int rc = halo_exchange(r, ovl, ovl)) return rc;
+        // (peer-memory path: the producer of r already pushed those rows into the neighbours' arenas, make_push())
+        if (!p2p)
+            if (int rc = halo_exchange(r, ovl, ovl)) return rc;
         TR("r halo");
+        // 16-byte accesses when a grid row is a multiple of 16 bytes (always true on the peer-memory path)
+        constexpr int kVec = 16 / (int)sizeof(Real);
+        const bool bvec = ((size_t)sy * sizeof(Real)) % 16 == 0;
+#define LAUNCH_BAND(kern, ...) do { if (bvec) LAUNCH((kern<Real, kVec>), __VA_ARGS__); else LAUNCH((kern<Real, 1>), __VA_ARGS__); } while (0)
         struct Band { int ja, jb, peer; };
         Band bands[2] = {{g.j0 - ovl, g.j0 + ovl, rank - 1}, {g.j1 - ovl, g.j1 + ovl, rank + 1}};
         const bool has[2] = {rank > 0, rank + 1 < world};
-        const unsigned int bb = (unsigned int)std::min<long long>(kMgBlocks, (2 * (long long)brow + 255) / 256);
+        // band kernels: few blocks (each ends with a system-scope fence when it pushes to a peer), grid-stride
+        const unsigned int bb = (unsigned int)std::min<long long>(2 * kSMs, (2 * (long long)brow + 255) / 256);
         for (int b = 0; b < 2; ++b)
-            if (has[b]) LAUNCH((k_band_scale<Real>), bb, 256, S, sy, bands[b].ja, bands[b].jb, g.j0, g.j1, d_sw, r, band_save[b]);
+            if (has[b]) {
+                if (p2p) LAUNCH_BAND(k_band_scale, bb, 256, S, sy, bands[b].ja, bands[b].jb, g.j0, g.j1, d_sw, r, band_save[b],
+                                (const Real*)(arena + off_halo[b]), b == 0 ? g.j0 - ovl : g.j1, (const unsigned long long*)&head_of(rank)->flag[0][b], r_seq);
+                else LAUNCH_BAND(k_band_scale, bb, 256, S, sy, bands[b].ja, bands[b].jb, g.j0, g.j1, d_sw, r, band_save[b], (const Real*)nullptr, 0,
+                            (const unsigned long long*)nullptr, 0ull);
+            }
         TR("band scale");
         if (int rc = mg_vcycle(r)) return rc;
         TR("vcycle");
         Real* z = lv[0].xa;
+        const unsigned long long z_seq = p2p ? ++p2p_seq[1] : 0ull;
         for (int b = 0; b < 2; ++b)
-            if (has[b]) LAUNCH((k_band_restore_weight<Real>), bb, 256, S, sy, bands[b].ja, bands[b].jb, g.j0, g.j1, d_sw, r, band_save[b], z);
+            if (has[b]) {
+                if (p2p) LAUNCH_BAND(k_band_restore_weight, bb, 256, S, sy, bands[b].ja, bands[b].jb, g.j0, g.j1, d_sw, r, band_save[b], z,
+                                (Real*)(peers.base[bands[b].peer] + off_band[1 - b]), &head_of(bands[b].peer)->flag[1][1 - b], z_seq, &head_of(rank)->ticket[2 + b]);
+                else LAUNCH_BAND(k_band_restore_weight, bb, 256, S, sy, bands[b].ja, bands[b].jb, g.j0, g.j1, d_sw, r, band_save[b], z, (Real*)nullptr,
+                            (unsigned long long*)nullptr, 0ull, (unsigned int*)nullptr);
+            }
         CK(cudaGetLastError());
         TR("band weight");
         const Real* recv[2] = {band_recv[0], band_recv[1]};
-        if (p2p) {   // weighted z on both 2*ovl-row bands straight into the neighbours' arenas; combine reads it there
-            if (int rc = p2p_band(1, off_band, z, g.j0 - ovl, g.j1 - ovl, 2 * ovl, nullptr, 0, 0)) return rc;
+        if (p2p) {   // the weighted bands are already in the neighbours' arenas (k_band_restore_weight pushed them); combine waits for ours
             recv[0] = reinterpret_cast<const Real*>(arena + off_band[0]);
             recv[1] = reinterpret_cast<const Real*>(arena + off_band[1]);
         } else {
@@ -1170,7 +1200,9 @@ struct Ctx final : CtxBase {
             NK(nccl().GroupEnd());
         }
         for (int b = 0; b < 2; ++b)
-            if (has[b]) LAUNCH((k_band_combine<Real>), bb, 256, S, sy, bands[b].ja, bands[b].jb, g.j0, g.j1, recv[b], r, z);
+            if (has[b]) LAUNCH_BAND(k_band_combine, bb, 256, S, sy, bands[b].ja, bands[b].jb, g.j0, g.j1, recv[b], r, z,
+                               p2p ? (const unsigned long long*)&head_of(rank)->flag[1][b] : (const unsigned long long*)nullptr, z_seq);
+#undef LAUNCH_BAND
         TR("z band combine");
         CK(cudaGetLastError());
         return 0;
@@ -1189,8 +1221,9 @@ struct Ctx final : CtxBase {
         const bool dist = world > 1;
         const int hlo = (dist && rank > 0) ? 1 : 0, hhi = (dist && rank + 1 < world) ? 1 : 0;
         if (int rc = halo_exchange(x, 1, 1)) return rc;     // warm start: the initial residual needs x on the neighbour rows
-        if (vec4()) LAUNCH((k_cg_init<Real, 4>), nb, 256, g, S, f, x, cg_r);
-        else LAUNCH((k_cg_init<Real, 1>), nb, 256, g, S, f, x, cg_r);
+        { const P2pPush push = make_push();
+          if (vec4()) LAUNCH((k_cg_init<Real, 4>), nb, 256, g, S, f, x, cg_r, push);
+          else LAUNCH((k_cg_init<Real, 1>), nb, 256, g, S, f, x, cg_r, push); }
         CK(cudaGetLastError());
         if (dist) {
             if (int rc = ar_post(0, 4, 0)) return rc;
@@ -1229,12 +1262,13 @@ struct Ctx final : CtxBase {
                     if (int rc = ar_post(0, 1, 1)) return rc;
                 }
                 TR("allreduce dw");
+                const P2pPush push = make_push();
                 if (vec4()) {
-                    if (use_mg) LAUNCH((k_cg_update<Real, 4, true>), nb, 256, g, S, x, cg_r, cg_d[dcur ^ 1], cg_w);
-                    else LAUNCH((k_cg_update<Real, 4, false>), nb, 256, g, S, x, cg_r, cg_d[dcur ^ 1], cg_w);
+                    if (use_mg) LAUNCH((k_cg_update<Real, 4, true>), nb, 256, g, S, x, cg_r, cg_d[dcur ^ 1], cg_w, push);
+                    else LAUNCH((k_cg_update<Real, 4, false>), nb, 256, g, S, x, cg_r, cg_d[dcur ^ 1], cg_w, push);
                 } else {
-                    if (use_mg) LAUNCH((k_cg_update<Real, 1, true>), nb, 256, g, S, x, cg_r, cg_d[dcur ^ 1], cg_w);
-                    else LAUNCH((k_cg_update<Real, 1, false>), nb, 256, g, S, x, cg_r, cg_d[dcur ^ 1], cg_w);
+                    if (use_mg) LAUNCH((k_cg_update<Real, 1, true>), nb, 256, g, S, x, cg_r, cg_d[dcur ^ 1], cg_w, push);
+                    else LAUNCH((k_cg_update<Real, 1, false>), nb, 256, g, S, x, cg_r, cg_d[dcur ^ 1], cg_w, push);
                 }
                 TR("update");
                 if (use_mg)

@@ -37,6 +37,22 @@ INK_HD Pack<Real, V> ldp(const Real* p) { return *reinterpret_cast<const Pack<Re
 template <class Real, int V>
 INK_HD void stp(Real* p, const Pack<Real, V>& v) { *reinterpret_cast<Pack<Real, V>*>(p) = v; }
 
+// Multi-GPU: a kernel that produces boundary rows can PUSH them straight into the neighbours' arenas (p2p.cuh) while it
+// writes them locally, and its last block publishes the sequence number: no separate put kernel on the critical path.
+// Cell offsets are relative to the first cell of this rank's slab; [0, lo_cells) goes to rank-1, [hi_start, ...) to rank+1.
+struct P2pPush {
+    int on;
+    long long lo_cells, hi_start;
+    void* dst_lo; void* dst_hi;                       // peer arena payload regions (nullptr = no neighbour on that side)
+    unsigned long long* flag_lo; unsigned long long* flag_hi;
+    unsigned long long seq;
+};
+__device__ __forceinline__ void p2p_publish(const P2pPush& p) {   // by ONE thread, after every block's stores were fenced system-wide
+    __threadfence_system();
+    if (p.dst_lo) *reinterpret_cast<volatile unsigned long long*>(p.flag_lo) = p.seq;
+    if (p.dst_hi) *reinterpret_cast<volatile unsigned long long*>(p.flag_hi) = p.seq;
+}
+
 // block-level fp64 sum -> S->partial[slot][block]; the last block to arrive adds all partials in a fixed order
 // and returns true (thread 0 of that block holds the total in `total`).
 __device__ __forceinline__ bool block_sum_last(double acc, CgScal* S, int slot, double& total) {
@@ -79,11 +95,12 @@ __device__ __forceinline__ void vec_cell(const Grid& g, long long t, int ZV, int
 
 // r = f - M x, <r,r>, <f,f>;  (x may be a warm start)
 template <class Real, int V>
-__global__ void __launch_bounds__(256) k_cg_init(Grid g, CgScal* S, const Real* __restrict__ f, const Real* __restrict__ x, Real* __restrict__ r) {
+__global__ void __launch_bounds__(256) k_cg_init(Grid g, CgScal* S, const Real* __restrict__ f, const Real* __restrict__ x, Real* __restrict__ r, P2pPush push) {
     INK_PDL();
     const int ZV = g.Z / V;
     const long long nvec = (long long)(g.j1 - g.j0) * g.X * ZV;
     double arr = 0, abb = 0;
+    bool pushed = false;
     for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < nvec; t += (long long)gridDim.x * blockDim.x) {
         int i, j, k; long long c;
         vec_cell<Real, V>(g, t, ZV, i, j, k, c);
@@ -116,7 +133,13 @@ __global__ void __launch_bounds__(256) k_cg_init(Grid g, CgScal* S, const Real* 
             abb += (double)fc.a[a] * (double)fc.a[a];
         }
         stp<Real, V>(r + c, rc);
+        if (push.on) {
+            const long long off = c - (long long)g.j0 * g.sy;
+            if (push.dst_lo && off < push.lo_cells) { stp<Real, V>(reinterpret_cast<Real*>(push.dst_lo) + off, rc); pushed = true; }
+            if (push.dst_hi && off >= push.hi_start) { stp<Real, V>(reinterpret_cast<Real*>(push.dst_hi) + (off - push.hi_start), rc); pushed = true; }
+        }
     }
+    if (pushed) __threadfence_system();   // only the threads that stored to a peer pay the system-scope fence (before the block's ticket)
     double tot_rr, tot_bb = 0;
     // two reductions through the same ticket: do <f,f> first via slot 1 without the ticket (plain partials)
     {
@@ -137,6 +160,7 @@ __global__ void __launch_bounds__(256) k_cg_init(Grid g, CgScal* S, const Real* 
             for (int q = lane; q < (int)gridDim.x; q += 32) s += __ldcg(&S->partial[1][q]);
             tot_bb = warp_sum(s);
             if (lane == 0) {
+                if (push.on) p2p_publish(push);
                 if (S->dist) { S->loc[1] = tot_rr; S->loc[3] = tot_bb; S->loc[0] = 0; S->loc[2] = 0; }
                 else {
                     S->rr = tot_rr; S->rr_old = tot_rr; S->bb = tot_bb; S->dw = 0;
@@ -215,7 +239,7 @@ __global__ void __launch_bounds__(256) k_cg_dir_matvec(Grid g, CgScal* S, const 
 // PRECOND: z = B r is produced by the V-cycle that follows (mg.cuh), which also sets rz / rz_old
 template <class Real, int V, bool PRECOND>
 __global__ void __launch_bounds__(256) k_cg_update(Grid g, CgScal* S, Real* __restrict__ x, Real* __restrict__ r, const Real* __restrict__ d,
-                                                   const Real* __restrict__ w) {
+                                                   const Real* __restrict__ w, P2pPush push) {
     INK_PDL();
     if (S->done) return;
     const Real alpha = (Real)(S->rz / S->dw);
@@ -223,6 +247,7 @@ __global__ void __launch_bounds__(256) k_cg_update(Grid g, CgScal* S, Real* __re
     const long long nvec = (long long)(g.j1 - g.j0) * g.X * ZV;
     const long long base = (long long)g.j0 * g.sy;
     double acc = 0;
+    bool pushed = false;
     for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < nvec; t += (long long)gridDim.x * blockDim.x) {
         const long long c = base + t * V;
         Pack<Real, V> xc = ldp<Real, V>(x + c), rc = ldp<Real, V>(r + c);
@@ -235,10 +260,17 @@ __global__ void __launch_bounds__(256) k_cg_update(Grid g, CgScal* S, Real* __re
         }
         stp<Real, V>(x + c, xc);
         stp<Real, V>(r + c, rc);
+        if (push.on) {
+            const long long off = t * V;
+            if (push.dst_lo && off < push.lo_cells) { stp<Real, V>(reinterpret_cast<Real*>(push.dst_lo) + off, rc); pushed = true; }
+            if (push.dst_hi && off >= push.hi_start) { stp<Real, V>(reinterpret_cast<Real*>(push.dst_hi) + (off - push.hi_start), rc); pushed = true; }
+        }
     }
+    if (pushed) __threadfence_system();   // only the threads that stored to a peer pay the system-scope fence (before the block's ticket)
     double tot;
     if (block_sum_last(acc, S, 1, tot)) {
         if (threadIdx.x == 0) {
+            if (push.on) p2p_publish(push);
             if (S->dist) S->loc[1] = tot;
             else {
                 S->rr_old = S->rr;

@@ -76,6 +76,16 @@ __device__ __forceinline__ float warp_max(float v) {
 
 constexpr int kSMs = 148;  // B200
 
+// spin until a sequence number published by a PEER GPU (p2p.cuh) has reached `want`; then order the payload reads after it
+__device__ __forceinline__ void p2p_spin(const volatile unsigned long long* flag, unsigned long long want) {
+    while (*flag < want) {
+#if defined(__CUDA_ARCH__) && __CUDA_ARCH__ >= 700
+        __nanosleep(64);
+#endif
+    }
+    __threadfence_system();
+}
+
 // Programmatic dependent launch (sm_90+).  The step is a chain of ~300 short kernels on one stream; with plain launches
 // each pays the full launch + drain latency (2-3 us, which is most of a coarse multigrid level's kernel).  Every kernel
 // of the library therefore starts with INK_PDL(): griddepcontrol.wait blocks until the PRECEDING kernel has completed

@@ -26,7 +26,8 @@
 
 namespace ink {
 
-constexpr int kMg3CoarsestCells = 1024;   // stop coarsening at <= this many cells (prototype: same iteration count as 16)
+constexpr int kMg3CoarsestCells = 2048;   // stop coarsening at <= this many cells (prototype: same iteration count as 16); 2048 so that
+                                          // a 1024-cell level widened by the multi-GPU overlap rows (1088 cells) is still the coarsest
 
 // res = r - (omega/6) M r
 template <class Real>

@@ -182,47 +182,94 @@ __global__ void __launch_bounds__(256) k_mg_residual_restrict_v4(const CgScal* S
 // W_i = partition of unity ramping linearly across the 2*ovl-row band around an interface (sw[j] = sqrt(W_i(j)) for
 // this rank).  SPD and symmetric; at ovl = 8 it converges like the global V-cycle for two boundary-row
 // exchanges per iteration instead of ~5 per level.  All three kernels run over one band of rows [ja, jb).
-template <class Real>
+// VEC = elements per access (16 bytes when a row is a multiple of 16 bytes — always on the peer-memory path — else 1).
+// t runs over the band in units of VEC elements; a band is < 2^31 cells.
+template <class Real, int VEC>
 __global__ void __launch_bounds__(256) k_band_scale(const CgScal* S, long long sy, int ja, int jb, int own0, int own1, const Real* __restrict__ sw,
-                                                    Real* __restrict__ r, Real* __restrict__ save) {
+                                                    Real* __restrict__ r, Real* __restrict__ save, const Real* halo_src, int halo_j0,
+                                                    const unsigned long long* wait_flag, unsigned long long seq) {
     INK_PDL();
     if (S->done) return;
-    const long long n = (long long)(jb - ja) * sy;
-    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) {
-        const int j = ja + (int)(t / sy);
-        const long long c = (long long)ja * sy + t;
-        const Real v = r[c];
-        if (j >= own0 && j < own1) save[t] = v;   // own rows are restored after the cycle; neighbour rows are scratch
-        r[c] = v * sw[j];
+    // peer-memory path: the neighbour's rows were pushed into this rank's arena by the kernel that produced them (P2pPush);
+    // wait for its sequence number, then take them from there (L2) instead of from r
+    if (wait_flag) {
+        if (threadIdx.x == 0) p2p_spin(reinterpret_cast<const volatile unsigned long long*>(wait_flag), seq);
+        __syncthreads();
+    }
+    const unsigned int syv = (unsigned int)(sy / VEC), n = (unsigned int)(jb - ja) * syv;
+    for (unsigned int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
+        const unsigned int jr = t / syv;
+        const int j = ja + (int)jr;
+        const long long e = (long long)t * VEC, c = (long long)ja * sy + e;
+        Pack<Real, VEC> v;
+        if (j >= own0 && j < own1) { v = ldp<Real, VEC>(r + c); stp<Real, VEC>(save + e, v); }   // own rows are restored after the cycle
+        else if (halo_src) {
+            const Real* hp = halo_src + ((long long)(j - halo_j0) * sy + (e - (long long)jr * sy));
+#pragma unroll
+            for (int a = 0; a < VEC; ++a) v.a[a] = __ldcg(hp + a);
+        } else v = ldp<Real, VEC>(r + c);
+        const Real w = sw[j];
+#pragma unroll
+        for (int a = 0; a < VEC; ++a) v.a[a] *= w;
+        stp<Real, VEC>(r + c, v);
     }
 }
-template <class Real>
+template <class Real, int VEC>
 __global__ void __launch_bounds__(256) k_band_restore_weight(const CgScal* S, long long sy, int ja, int jb, int own0, int own1, const Real* __restrict__ sw,
-                                                             Real* __restrict__ r, const Real* __restrict__ save, Real* __restrict__ z) {
+                                                             Real* __restrict__ r, const Real* __restrict__ save, Real* __restrict__ z, Real* push_dst,
+                                                             unsigned long long* push_flag, unsigned long long seq, unsigned int* ticket) {
     INK_PDL();
     if (S->done) return;
-    const long long n = (long long)(jb - ja) * sy;
-    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) {
-        const int j = ja + (int)(t / sy);
-        const long long c = (long long)ja * sy + t;
-        if (j >= own0 && j < own1) r[c] = save[t];
-        z[c] *= sw[j];
+    const unsigned int syv = (unsigned int)(sy / VEC), n = (unsigned int)(jb - ja) * syv;
+    for (unsigned int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
+        const int j = ja + (int)(t / syv);
+        const long long e = (long long)t * VEC, c = (long long)ja * sy + e;
+        if (j >= own0 && j < own1) stp<Real, VEC>(r + c, ldp<Real, VEC>(save + e));
+        Pack<Real, VEC> zz = ldp<Real, VEC>(z + c);
+        const Real w = sw[j];
+#pragma unroll
+        for (int a = 0; a < VEC; ++a) zz.a[a] *= w;
+        stp<Real, VEC>(z + c, zz);
+        if (push_dst) stp<Real, VEC>(push_dst + e, zz);   // peer-memory path: the weighted band goes straight into the neighbour's arena
+    }
+    if (push_dst) {   // last block to finish publishes the sequence number (every block fenced its remote stores first)
+        __threadfence_system();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            if (atomicAdd(ticket, 1u) == gridDim.x - 1) {
+                *ticket = 0;
+                __threadfence_system();
+                *reinterpret_cast<volatile unsigned long long*>(push_flag) = seq;
+            }
+        }
     }
 }
 // z += the neighbour's contribution on the band; adds <r, z> over this rank's own band rows to S->loc[2]
-template <class Real>
-__global__ void __launch_bounds__(256) k_band_combine(CgScal* S, long long sy, int ja, int jb, int own0, int own1, const Real* __restrict__ recv,
-                                                      const Real* __restrict__ r, Real* __restrict__ z) {
+template <class Real, int VEC>
+__global__ void __launch_bounds__(256) k_band_combine(CgScal* S, long long sy, int ja, int jb, int own0, int own1, const Real* recv,
+                                                      const Real* __restrict__ r, Real* __restrict__ z, const unsigned long long* wait_flag,
+                                                      unsigned long long seq) {
     INK_PDL();
     if (S->done) return;
-    const long long n = (long long)(jb - ja) * sy;
+    if (wait_flag) {   // peer-memory path: recv is this rank's arena, filled by the neighbour's k_band_restore_weight
+        if (threadIdx.x == 0) p2p_spin(reinterpret_cast<const volatile unsigned long long*>(wait_flag), seq);
+        __syncthreads();
+    }
+    const unsigned int syv = (unsigned int)(sy / VEC), n = (unsigned int)(jb - ja) * syv;
     double acc = 0;
-    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) {
-        const int j = ja + (int)(t / sy);
-        const long long c = (long long)ja * sy + t;
-        const Real v = z[c] + recv[t];
-        z[c] = v;
-        if (j >= own0 && j < own1) acc += (double)r[c] * (double)v;
+    for (unsigned int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
+        const int j = ja + (int)(t / syv);
+        const long long e = (long long)t * VEC, c = (long long)ja * sy + e;
+        Pack<Real, VEC> v = ldp<Real, VEC>(z + c);
+        const bool own = (j >= own0 && j < own1);
+        Pack<Real, VEC> rc;
+        if (own) rc = ldp<Real, VEC>(r + c);
+#pragma unroll
+        for (int a = 0; a < VEC; ++a) {
+            v.a[a] += __ldcg(recv + e + a);
+            if (own) acc += (double)rc.a[a] * (double)v.a[a];
+        }
+        stp<Real, VEC>(z + c, v);
     }
     double tot;
     if (block_sum_last(acc, S, 1, tot)) {

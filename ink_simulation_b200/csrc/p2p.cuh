@@ -38,11 +38,6 @@ struct P2pPeers {
     unsigned char* base[kP2pMaxRanks];      // arena of every rank as mapped in THIS process (own arena at [rank])
 };
 
-__device__ __forceinline__ void p2p_spin(const volatile unsigned long long* flag, unsigned long long want) {
-    while (*flag < want) { __nanosleep(64); }
-    __threadfence_system();
-}
-
 // ---- scalar all-reduce (sum of `count` <= 4 doubles starting at S->loc[off]) fused with the CG scalar epilogue ---------
 // One warp: lane p < world stores this rank's partials into rank p's mailbox, then waits for rank p's partials in the
 // local mailbox; lane 0 adds them in rank order (identical result on every rank) and applies k_cg_post's logic.
