@@ -6,6 +6,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -1031,8 +1032,15 @@ struct Ctx final : CtxBase {
                 mg_alloc.push_back(*slots[a]);
             }
         }
-        CK(cudaFuncSetAttribute(k_mg_tail<Real>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mg_tail_smem));
-        CK(cudaFuncSetAttribute(k_mg3_tail<Real>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mg_tail_smem));
+        // The attribute belongs to the FUNCTION, not to this context object: several Systems of different sizes may live in one
+        // process (tests/mgpu_check.py: a distributed and a single-GPU one), and a later, smaller one must not lower the limit
+        // under an earlier one's launches ("invalid argument").  Keep a process-wide running maximum, never below the default.
+        static std::atomic<size_t> tail_attr{48 * 1024};
+        size_t want = tail_attr.load();
+        while (want < mg_tail_smem && !tail_attr.compare_exchange_weak(want, mg_tail_smem)) {}
+        want = std::max(want, mg_tail_smem);
+        CK(cudaFuncSetAttribute(k_mg_tail<Real>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)want));
+        CK(cudaFuncSetAttribute(k_mg3_tail<Real>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)want));
         // Persistent coarse-level kernel: OFF by default.  Measured on B200 (128x256x128): 63 us for levels 2..4 in one launch
         // (7 device-side grid barriers, 32 blocks) against ~40 us for the same levels as 10 PDL-chained launches that use the
         // whole GPU; step 2.35 vs 1.97 ms.  Kept opt-in (INK_MG_COARSE=1) as the starting point for a cluster/DSMEM version.
@@ -1045,7 +1053,7 @@ struct Ctx final : CtxBase {
             if (mg_lc >= 1) {
                 CK(cudaMalloc(&mg_bar, 2 * sizeof(unsigned int)));
                 CK(cudaMemsetAsync(mg_bar, 0, 2 * sizeof(unsigned int), stream));
-                CK(cudaFuncSetAttribute(k_mg3_coarse<Real>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mg_tail_smem));
+                CK(cudaFuncSetAttribute(k_mg3_coarse<Real>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)want));
             }
         }
         use_mg = true;

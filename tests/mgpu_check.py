@@ -35,7 +35,10 @@ def main():
         if not ok:
             failures.append(f"rank {rank}: {name} {info}")
 
-    for dims, npart in (((16, 5 * world, 12), 5000), ((16, 40, 12), 20000), ((32, 64, 32), 200000)):
+    cases = (((16, 5 * world, 12), 5000), ((16, 40, 12), 20000), ((32, 64, 32), 200000))
+    if os.environ.get("MGPU_CASES"):   # e.g. MGPU_CASES=0,2: run a subset (debugging at large world sizes)
+        cases = tuple(cases[int(i)] for i in os.environ["MGPU_CASES"].split(","))
+    for dims, npart in cases:
         u, v, w = util.rand_field(dims, 11, scale=0.5)
         part = util.uniform_particles(dims, npart, 12)
         lo, hi = shard_range(npart, rank, world)

@@ -261,3 +261,23 @@ def test_gpu_streaming_io_equals_blocking_io():
         C_.set_particles(inputs[s])
         C_.solve(0.35)
         np.testing.assert_array_equal(outs[s].numpy(), C_.get_particles()[0])
+
+
+def test_gpu_two_systems_of_different_size_in_one_process():
+    """A System whose whole grid is the multigrid tail (23 KB of shared memory) must keep working after a second System with
+    a much smaller tail is created: the shared-memory limit is a property of the kernel, not of the System (regression:
+    'invalid argument' at 4 ranks in tests/mgpu_check.py, where a distributed and a single-GPU System share a process)."""
+    dims_a, dims_b = (16, 10, 12), (16, 20, 12)
+    A = gpu(dims_a)
+    ref = gpu(dims_a)
+    u, v, w = util.rand_field(dims_a, 21, scale=0.5)
+    for T in (A, ref):
+        T.set_velocity(u, v, w)
+    ref.pressure(0.17)
+    B = gpu(dims_b)          # created AFTER A, smaller tail
+    B.set_velocity(*util.rand_field(dims_b, 22, scale=0.5))
+    B.pressure(0.17)
+    A.pressure(0.17)
+    assert np.array_equal(np.stack(A.get_velocity()), np.stack(ref.get_velocity()))
+    for T in (A, B, ref):
+        T.close()
