@@ -94,6 +94,12 @@ int  ink_set_velocity(ink_ctx* c, const void* u, const void* v, const void* w, i
 int  ink_get_field(ink_ctx* c, int which, void* u, void* v, void* w, int host_dtype);
 int  ink_get_pressure(ink_ctx* c, void* p, int host_dtype);
 int  ink_set_pressure(ink_ctx* c, const void* p, int host_dtype);   /* warm-start seed / pressure_given tests */
+/* The Poisson solver's own unknown q = p - p_atm exactly as it is held (the start vector of the next solve when
+ * cg_warm_start = 1).  For checkpoints: p = q + p_atm has lost q's low bits, so a run restored through ink_set_pressure
+ * continues within the solver tolerance, one restored through ink_set_warm_start continues bit for bit.  No reference
+ * equivalent (SparseLU has no state); SURVEY 8f-3 "matching load". */
+int  ink_get_warm_start(ink_ctx* c, void* q, int host_dtype);
+int  ink_set_warm_start(ink_ctx* c, const void* q, int host_dtype);
 int  ink_get_mark(ink_ctx* c, uint8_t* mark);           /* force mask of the last forces phase */
 int  ink_get_divergence(ink_ctx* c, void* div, int host_dtype);  /* getDivergence on oldVelocity, src/systemHelpers.cpp:30-43 */
 int  ink_sample_velocity(ink_ctx* c, const void* pos_xyz, int64_t n, void* out_xyz, int host_dtype); /* getVelocity :110-115 */

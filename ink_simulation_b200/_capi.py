@@ -52,6 +52,8 @@ SYMBOLS = {
     "ink_get_field": (_I, [_VP, _I, _VP, _VP, _VP, _I]),
     "ink_get_pressure": (_I, [_VP, _VP, _I]),
     "ink_set_pressure": (_I, [_VP, _VP, _I]),
+    "ink_get_warm_start": (_I, [_VP, _VP, _I]),
+    "ink_set_warm_start": (_I, [_VP, _VP, _I]),
     "ink_get_mark": (_I, [_VP, _VP]),
     "ink_get_divergence": (_I, [_VP, _VP, _I]),
     "ink_sample_velocity": (_I, [_VP, _VP, _L, _VP, _I]),

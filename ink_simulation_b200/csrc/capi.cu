@@ -89,6 +89,8 @@ struct CtxBase {
     virtual int get_field(int which, void* u, void* v, void* w, int dt) = 0;
     virtual int get_pressure(void* p, int dt) = 0;
     virtual int set_pressure(const void* p, int dt) = 0;
+    virtual int get_warm_start(void* q, int dt) = 0;
+    virtual int set_warm_start(const void* q, int dt) = 0;
     virtual int get_mark(uint8_t* m) = 0;
     virtual int get_divergence(void* d, int dt) = 0;
     virtual int sample_velocity(const void* pos, int64_t n, void* out, int dt) = 0;
@@ -811,6 +813,19 @@ struct Ctx final : CtxBase {
         have_q = true;
         return 0;
     }
+    // the Poisson solver's own unknown q = p - p_atm, exactly as held (checkpoints: p has lost the low bits of q to the +p_atm)
+    int get_warm_start(void* qo, int hd) override {   // multi-GPU: collective
+        if (int rc = check_hd(hd, err)) return rc;
+        if (!have_q) CK(cudaMemsetAsync(q, 0, (size_t)g.n * sizeof(Real), stream));
+        if (int rc = allgather_rows(q, sizeof(Real))) return rc;
+        return grid_out_any(q, qo, hd);
+    }
+    int set_warm_start(const void* qi, int hd) override {
+        if (int rc = check_hd(hd, err)) return rc;
+        if (int rc = grid_in_any(qi, q, hd)) return rc;
+        have_q = true;
+        return 0;
+    }
     int get_mark(uint8_t* m) override {
         if (int rc = need_stage((size_t)g.n * 8)) return rc;
         uint8_t* dst = is_device_ptr(m) ? m : (uint8_t*)stage;
@@ -1506,6 +1521,8 @@ int ink_set_velocity(ink_ctx* c, const void* u, const void* v, const void* w, in
 int ink_get_field(ink_ctx* c, int which, void* u, void* v, void* w, int hd) { return c->impl->get_field(which, u, v, w, hd); }
 int ink_get_pressure(ink_ctx* c, void* p, int hd) { return c->impl->get_pressure(p, hd); }
 int ink_set_pressure(ink_ctx* c, const void* p, int hd) { return c->impl->set_pressure(p, hd); }
+int ink_get_warm_start(ink_ctx* c, void* q, int hd) { return c->impl->get_warm_start(q, hd); }
+int ink_set_warm_start(ink_ctx* c, const void* q, int hd) { return c->impl->set_warm_start(q, hd); }
 int ink_get_mark(ink_ctx* c, uint8_t* m) { return c->impl->get_mark(m); }
 int ink_get_divergence(ink_ctx* c, void* d, int hd) { return c->impl->get_divergence(d, hd); }
 int ink_sample_velocity(ink_ctx* c, const void* pos, int64_t n, void* out, int hd) { return c->impl->sample_velocity(pos, n, out, hd); }

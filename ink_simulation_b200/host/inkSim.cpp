@@ -11,8 +11,11 @@
 #include <chrono>
 #include <cstdio>
 #include <ctime>
+#include <cstdint>
+#include <cstring>
 #include <filesystem>
 #include <stdexcept>
+#include <algorithm>
 
 #include <cuda_runtime_api.h>
 
@@ -49,8 +52,9 @@ void InkSim::simulate(const float renderTimestep, int totalTimesteps) {
     std::cout << "\033[32mSimulation started at: \033[m" << std::ctime(&startTime) << std::endl;
 
     int timestepCounter = 1;
-    int currFrame = 1;
-    float timeSinceLastRender = 0;
+    int currFrame = m_resumed ? m_nextFrame : 1;
+    float timeSinceLastRender = m_resumed ? m_timeSinceLastRender : 0;
+    m_resumed = false;
     while (timestepCounter <= totalTimesteps) {
         float timeStep = this->ink_system.solve(renderTimestep - timeSinceLastRender);
         timeSinceLastRender += timeStep;
@@ -63,6 +67,8 @@ void InkSim::simulate(const float renderTimestep, int totalTimesteps) {
     }
     drain();
     writeWaterGridVelocities();
+    m_nextFrame = currFrame;
+    m_timeSinceLastRender = timeSinceLastRender;
 
     auto endTS = std::chrono::system_clock::now();
     std::chrono::duration<double> elapsed_seconds = endTS - startTS;
@@ -117,32 +123,155 @@ void InkSim::writeToFile(int frameNum) {
     });
 }
 
-void InkSim::writeWaterGridVelocities() {
-    std::string filename = this->writeDirectory + "/" + "velocityField.ply";
-    std::cout << "writing to: " + filename << std::endl;
-    const size_t n = (size_t)WATERGRID_X * WATERGRID_Y * WATERGRID_Z;
-    std::string numVectors = std::to_string(n);
-    std::cout << "recording " + numVectors + " velocities" << std::endl;
-    std::string header = "ply\n"
-                         "format binary_small_endian 1.0\n"
-                         "element vertex " + numVectors + "\n"
-                         "property float x\n"
-                         "property float y\n"
-                         "property float z\n"
-                         "property float u\n"
-                         "property float v\n"
-                         "property float w\n"
-                         "end_header\n";
-    std::vector<float> u(n), v(n), w(n), rec(6 * n);
-    ink_system.copyVelocityField(u.data(), v.data(), w.data());
+// header of a dump with `props` float properties per record; the first three are always x y z
+static std::string ply_header(size_t n, const std::vector<std::string>& props) {
+    std::string h = "ply\n"
+                    "format binary_small_endian 1.0\n"
+                    "element vertex " + std::to_string(n) + "\n";
+    for (const std::string& p : props) h += "property float " + p + "\n";
+    return h + "end_header\n";
+}
+
+// (cx, cy, cz, f0[, f1, f2]) per cell in i-j-k order, centre = index + h/2 (src/inkSim.cpp:137-141)
+static void write_grid_ply(const std::string& filename, const std::vector<std::string>& names, const std::vector<const float*>& f) {
+    const size_t n = (size_t)WATERGRID_X * WATERGRID_Y * WATERGRID_Z, props = 3 + f.size();
+    std::vector<std::string> all = {"x", "y", "z"};
+    all.insert(all.end(), names.begin(), names.end());
+    std::vector<float> rec(props * n);
     const float offset = CELL_DIM / 2.f;
     size_t c = 0;
     for (int i = 0; i < WATERGRID_X; i++)
         for (int j = 0; j < WATERGRID_Y; j++)
             for (int k = 0; k < WATERGRID_Z; k++, c++) {
-                float* r = &rec[6 * c];
-                r[0] = i + offset; r[1] = j + offset; r[2] = k + offset;   // cell centre, src/inkSim.cpp:137-141
-                r[3] = u[c]; r[4] = v[c]; r[5] = w[c];
+                float* r = &rec[props * c];
+                r[0] = i + offset; r[1] = j + offset; r[2] = k + offset;
+                for (size_t a = 0; a < f.size(); ++a) r[3 + a] = f[a][c];
             }
-    write_blob(filename, header, rec.data(), rec.size());
+    write_blob(filename, ply_header(n, all), rec.data(), rec.size());
+}
+
+// Reader for every .ply this program writes (frames, velocityField.ply, checkpoint files): like render.py:290-294 it only
+// looks for "element vertex N" and "end_header", plus the number of "property float" lines; the payload is raw host-endian
+// fp32.  Returns the records (n x props) or throws.
+static std::vector<float> read_ply(const std::string& filename, size_t& n, size_t& props) {
+    FILE* f = std::fopen(filename.c_str(), "rb");
+    if (!f) throw std::runtime_error("cannot open " + filename);
+    std::string header;
+    n = 0; props = 0;
+    bool ended = false, have_n = false;
+    char line[512];
+    while (std::fgets(line, sizeof line, f)) {
+        const std::string ln(line);
+        if (ln.rfind("element vertex ", 0) == 0) { n = (size_t)std::stoull(ln.substr(15)); have_n = true; }
+        else if (ln.rfind("property float ", 0) == 0) props++;
+        else if (ln == "end_header\n") { ended = true; break; }
+    }
+    if (!ended || !have_n || props == 0) { std::fclose(f); throw std::runtime_error("not a ply dump of this program: " + filename); }
+    std::vector<float> rec(n * props);
+    const size_t got = std::fread(rec.data(), sizeof(float), rec.size(), f);
+    const bool extra = std::fgetc(f) != EOF;
+    std::fclose(f);
+    if (got != rec.size() || extra) throw std::runtime_error("payload size does not match the header: " + filename);
+    return rec;
+}
+
+// C hooks for the CPU-side tests (no GPU context involved)
+extern "C" long inkhost_read_ply(const char* filename, float* out, long cap_floats, int* props_out) {
+    try {
+        size_t n, props;
+        const std::vector<float> rec = read_ply(filename, n, props);
+        if (props_out) *props_out = (int)props;
+        if (out && (long)rec.size() <= cap_floats) std::copy(rec.begin(), rec.end(), out);
+        return (long)n;
+    } catch (const std::exception&) { return -1; }
+}
+extern "C" void inkhost_write_grid_ply(const char* filename, int nfields, const float* f0, const float* f1, const float* f2) {
+    static const char* vel[3] = {"u", "v", "w"};
+    std::vector<std::string> names;
+    std::vector<const float*> f;
+    const float* in[3] = {f0, f1, f2};
+    for (int a = 0; a < nfields && a < 3; ++a) { names.push_back(nfields == 1 ? "q" : vel[a]); f.push_back(in[a]); }
+    write_grid_ply(filename, names, f);
+}
+extern "C" void inkhost_grid_dims(int* xyz) { xyz[0] = WATERGRID_X; xyz[1] = WATERGRID_Y; xyz[2] = WATERGRID_Z; }
+
+void InkSim::writeWaterGridVelocities() {
+    std::string filename = this->writeDirectory + "/" + "velocityField.ply";
+    std::cout << "writing to: " + filename << std::endl;
+    const size_t n = (size_t)WATERGRID_X * WATERGRID_Y * WATERGRID_Z;
+    std::cout << "recording " + std::to_string(n) + " velocities" << std::endl;
+    std::vector<float> u(n), v(n), w(n);
+    ink_system.copyVelocityField(u.data(), v.data(), w.data());
+    write_grid_ply(filename, {"u", "v", "w"}, {u.data(), v.data(), w.data()});
+}
+
+// ---- checkpoint / resume ------------------------------------------------------------------------------------------------
+// State of a run between two steps = currVelocity (old == curr there, src/waterSolver.cpp:92-95), the particles, and — ours
+// only — the start vector of the next pressure solve.  Everything else the library keeps (force-mask seeds, max speed,
+// particle bins, curl) is recomputed from these, and none of it depends on the particle order in memory.
+void InkSim::writeCheckpoint() {
+    drain();
+    const std::string dir = this->writeDirectory + "/checkpoint";
+    std::filesystem::create_directories(dir);
+    const size_t n = (size_t)WATERGRID_X * WATERGRID_Y * WATERGRID_Z;
+    std::vector<float> u(n), v(n), w(n), q(n);
+    ink_system.copyVelocityField(u.data(), v.data(), w.data());
+    write_grid_ply(dir + "/velocityField.ply", {"u", "v", "w"}, {u.data(), v.data(), w.data()});
+    ink_system.copyWarmStart(q.data());
+    write_grid_ply(dir + "/warmstart.ply", {"q"}, {q.data()});
+    const int drops = ink_system.numDrops();
+    for (int d = 0; d < drops; d++) {
+        const size_t np = (size_t)ink_system.numParticles(d);
+        std::vector<float> pos(3 * np), vel(3 * np), rec(6 * np);
+        if (np) ink_system.copyParticles(d, pos.data(), vel.data());
+        for (size_t i = 0; i < np; i++)
+            for (int a = 0; a < 3; a++) { rec[6 * i + a] = pos[3 * i + a]; rec[6 * i + 3 + a] = vel[3 * i + a]; }
+        write_blob(dir + "/drop" + std::to_string(d) + ".ply", ply_header(np, {"x", "y", "z", "vx", "vy", "vz"}), rec.data(), rec.size());
+    }
+    uint32_t bits;
+    static_assert(sizeof bits == sizeof m_timeSinceLastRender, "float bits");
+    std::memcpy(&bits, &m_timeSinceLastRender, sizeof bits);
+    FILE* f = std::fopen((dir + "/meta.txt").c_str(), "w");
+    if (!f) throw std::runtime_error("cannot write " + dir + "/meta.txt");
+    std::fprintf(f, "grid %d %d %d\ndrops %d\nnext_frame %d\ntime_since_last_render_bits 0x%08x\n", WATERGRID_X, WATERGRID_Y, WATERGRID_Z, drops,
+                 m_nextFrame, bits);
+    std::fclose(f);
+}
+
+bool InkSim::resume() {
+    const std::string dir = this->writeDirectory + "/checkpoint";
+    FILE* f = std::fopen((dir + "/meta.txt").c_str(), "r");
+    if (!f) return false;
+    int X = 0, Y = 0, Z = 0, drops = 0, frame = 1;
+    unsigned int bits = 0;
+    const int got = std::fscanf(f, "grid %d %d %d drops %d next_frame %d time_since_last_render_bits 0x%x", &X, &Y, &Z, &drops, &frame, &bits);
+    std::fclose(f);
+    if (got != 6) throw std::runtime_error("malformed " + dir + "/meta.txt");
+    if (X != WATERGRID_X || Y != WATERGRID_Y || Z != WATERGRID_Z) throw std::runtime_error("checkpoint is for another grid size");
+    const size_t n = (size_t)X * Y * Z;
+    size_t cnt, props;
+    std::vector<float> rec = read_ply(dir + "/velocityField.ply", cnt, props);
+    if (cnt != n || props != 6) throw std::runtime_error("checkpoint velocityField.ply: wrong shape");
+    std::vector<float> u(n), v(n), w(n), q(n);
+    for (size_t c = 0; c < n; c++) { u[c] = rec[6 * c + 3]; v[c] = rec[6 * c + 4]; w[c] = rec[6 * c + 5]; }
+    rec = read_ply(dir + "/warmstart.ply", cnt, props);
+    if (cnt != n || props != 4) throw std::runtime_error("checkpoint warmstart.ply: wrong shape");
+    for (size_t c = 0; c < n; c++) q[c] = rec[4 * c + 3];
+    std::vector<std::vector<float>> pos(drops), vel(drops);
+    for (int d = 0; d < drops; d++) {   // read everything before touching the state
+        rec = read_ply(dir + "/drop" + std::to_string(d) + ".ply", cnt, props);
+        if (props != 6) throw std::runtime_error("checkpoint drop file: wrong shape");
+        pos[d].resize(3 * cnt); vel[d].resize(3 * cnt);
+        for (size_t i = 0; i < cnt; i++)
+            for (int a = 0; a < 3; a++) { pos[d][3 * i + a] = rec[6 * i + a]; vel[d][3 * i + a] = rec[6 * i + 3 + a]; }
+    }
+    ink_system.setVelocityField(u.data(), v.data(), w.data());
+    ink_system.setWarmStart(q.data());
+    for (int d = 0; d < drops; d++) ink_system.setInk(d, pos[d].data(), vel[d].data(), (long long)(pos[d].size() / 3));
+    float since;
+    std::memcpy(&since, &bits, sizeof since);
+    m_nextFrame = frame;
+    m_timeSinceLastRender = since;
+    m_resumed = true;
+    return true;
 }

@@ -98,3 +98,26 @@ extern "C" long inkhost_emitter_scene(int X, int Y, int Z, float* pos, float* ve
         for (int a = 0; a < 3; ++a) { pos[3 * i + a] = out[i].position[a]; vel[3 * i + a] = out[i].velocity[a]; }
     return n;
 }
+
+// one drop of n particles in the initParticles box, drawn the way a fresh process draws them: glibc rand() is never seeded
+// by the reference, i.e. the sequence of srand(1)
+extern "C" long inkhost_box_scene(int X, int Y, int Z, int n, float* pos, long cap) {
+    std::srand(1);
+    std::vector<std::vector<Particle>> drops;
+    inkseed::box(X, Y, Z, {n}, drops);
+    const long m = (long)drops[0].size();
+    for (long i = 0; i < m && i < cap; ++i)
+        for (int a = 0; a < 3; ++a) pos[3 * i + a] = drops[0][i].position[a];
+    return m;
+}
+
+// initFromFile: returns the particle count (call with cap = 0 to size the arrays), -1 if the file cannot be read
+extern "C" long inkhost_from_file(const char* path, float* pos, float* vel, long cap) {
+    try {
+        const std::vector<Particle> ink = inkseed::from_file(path);
+        const long n = (long)ink.size();
+        for (long i = 0; i < n && i < cap; ++i)
+            for (int a = 0; a < 3; ++a) { pos[3 * i + a] = ink[i].position[a]; vel[3 * i + a] = ink[i].velocity[a]; }
+        return n;
+    } catch (const std::exception&) { return -1; }
+}

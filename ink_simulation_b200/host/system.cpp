@@ -88,6 +88,31 @@ void System::copyVelocityField(float* u, float* v, float* w) {
     if (ink_get_field(m_ctx, INK_FIELD_CURR, u, v, w, 32) != 0) fail("ink_get_field");
 }
 
+// ---- checkpoint / resume -------------------------------------------------------------------------------------------------
+void System::copyParticles(int drop, float* xyz, float* vel) {
+    if (ink_get_particles(m_ctx, drop, xyz, vel, 32) != 0) fail("ink_get_particles");
+}
+void System::copyWarmStart(float* q) {
+    if (ink_get_warm_start(m_ctx, q, 32) != 0) fail("ink_get_warm_start");
+}
+void System::setVelocityField(const float* u, const float* v, const float* w) {
+    if (ink_set_velocity(m_ctx, u, v, w, 32) != 0) fail("ink_set_velocity");
+}
+void System::setWarmStart(const float* q) {
+    if (ink_set_warm_start(m_ctx, q, 32) != 0) fail("ink_set_warm_start");
+}
+void System::setInk(int drop, const float* xyz, const float* vel, long long n) {
+    if (drop < 0 || drop > (int)m_ink.size()) throw std::runtime_error("setInk: drop index out of range");
+    if (drop == (int)m_ink.size()) m_ink.emplace_back();
+    Particle blank;
+    blank.position = blank.velocity = Vector3f(0, 0, 0);
+    blank.opacity = 1.f;
+    blank.lifeTime = 5.f;
+    m_ink[drop].assign((size_t)n, blank);
+    if (ink_set_particles(m_ctx, drop, xyz, vel, (int64_t)n, 32) != 0) fail("ink_set_particles");
+    m_inkStale = true;   // the mirror is refilled from the device by the next getInkParticles()
+}
+
 const std::vector<std::vector<Particle>>& System::getInkParticles() {
     if (!m_inkStale) return m_ink;
     std::vector<float> pos, vel;

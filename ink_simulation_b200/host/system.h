@@ -119,6 +119,12 @@ public:
     // dense currVelocity, (X, Y, Z) C-order, three arrays of X*Y*Z floats
     void copyVelocityField(float* u, float* v, float* w);
     ink_ctx* handle() { return m_ctx; }
+    // checkpoint / resume (InkSim::writeCheckpoint / resume; SURVEY 8f-3 "matching load" of the velocity dump)
+    void copyParticles(int drop, float* xyz, float* vel);        // positions AND stored velocities (Q4)
+    void copyWarmStart(float* q);                                // the Poisson solver's start vector, X*Y*Z floats
+    void setVelocityField(const float* u, const float* v, const float* w);
+    void setWarmStart(const float* q);
+    void setInk(int drop, const float* xyz, const float* vel, long long n);   // replace (or append) one drop
 
 private:
     ink_ctx* m_ctx = nullptr;

@@ -239,6 +239,17 @@ class System:
         assert p.shape == self.dims
         self._ck(self.L.ink_set_pressure(self.h, _ptr(p), self.hd))
 
+    def get_warm_start(self):
+        """q = p - p_atm exactly as the Poisson solver holds it (ink_get_warm_start; checkpoints)."""
+        q = np.empty(self.dims, self.dtype)
+        self._ck(self.L.ink_get_warm_start(self.h, _ptr(q), self.hd))
+        return q
+
+    def set_warm_start(self, q):
+        q = self._a(q)
+        assert q.shape == self.dims
+        self._ck(self.L.ink_set_warm_start(self.h, _ptr(q), self.hd))
+
     def get_mark(self):
         m = np.empty(self.dims, np.uint8)
         self._ck(self.L.ink_get_mark(self.h, _ptr(m)))
