@@ -375,28 +375,6 @@ struct Ctx final : CtxBase {
         if (int rc = allreduce(S->loc + off, (size_t)count, ncclDouble, ncclSum)) return rc;
         return cg_post(stage);
     }
-    // channel ch: send rows [lo_src, +rows) to rank-1 and [hi_src, +rows) to rank+1 (into their regions at `off`), then wait for
-    // the neighbours' rows and (dst != nullptr) unpack them at lo_dst / hi_dst
-    int p2p_band(int ch, const size_t off[2], const Real* a, long long lo_src_row, long long hi_src_row, int rows, Real* dst, long long lo_dst_row,
-                 long long hi_dst_row) {
-        const unsigned long long seq = ++p2p_seq[ch];
-        const long long n16 = (long long)((size_t)rows * g.sy * sizeof(Real) / 16);
-        P2pPut pd{}; P2pGet gd{};
-        if (rank > 0) {
-            pd.src[0] = a + lo_src_row * g.sy; pd.dst[0] = peers.base[rank - 1] + off[1]; pd.flag[0] = &head_of(rank - 1)->flag[ch][1]; pd.n16[0] = n16;
-            gd.flag[0] = &head_of(rank)->flag[ch][0]; gd.src[0] = arena + off[0]; gd.dst[0] = dst ? dst + lo_dst_row * g.sy : nullptr; gd.n16[0] = n16;
-        }
-        if (rank + 1 < world) {
-            pd.src[1] = a + hi_src_row * g.sy; pd.dst[1] = peers.base[rank + 1] + off[0]; pd.flag[1] = &head_of(rank + 1)->flag[ch][0]; pd.n16[1] = n16;
-            gd.flag[1] = &head_of(rank)->flag[ch][1]; gd.src[1] = arena + off[1]; gd.dst[1] = dst ? dst + hi_dst_row * g.sy : nullptr; gd.n16[1] = n16;
-        }
-        const unsigned int nb = (unsigned int)std::min<long long>(kSMs, std::max<long long>(1, (n16 + 255) / 256));
-        LAUNCH(k_p2p_put, nb, 256, (const CgScal*)S, pd, seq, &head_of(rank)->ticket[ch]);
-        LAUNCH(k_p2p_wait_unpack, dst ? nb : 1u, 256, (const CgScal*)S, gd, seq);
-        CK(cudaGetLastError());
-        return 0;
-    }
-
     // boundary rows of the residual about to be produced (k_cg_init / k_cg_update) go straight into the neighbours' arenas
     P2pPush make_push() {
         P2pPush p{};

@@ -31,7 +31,7 @@ struct P2pHead {
     unsigned long long flag[4][2];          // [channel][side 0 = from rank-1, 1 = from rank+1] last sequence delivered
     unsigned long long mail_seq;            // LOCAL: all-reduces this rank has taken part in (kept on the device so that
                                             // calls skipped after convergence do not advance it)
-    unsigned int ticket[4];                 // LOCAL: block tickets of the put kernels
+    unsigned int ticket[4];                 // LOCAL: block tickets of the pushing band kernels ([2 + side])
 };
 
 struct P2pPeers {
@@ -90,61 +90,11 @@ __global__ void __launch_bounds__(32) k_p2p_allreduce_post(CgScal* S, P2pPeers p
     }
 }
 
-// ---- boundary-band put: copy up to two contiguous ranges into the two neighbours' arenas, then publish `seq` ------------
-struct P2pPut {
-    const void* src[2];       // local source (nullptr = no neighbour on that side)
-    void* dst[2];             // peer arena address of the payload region
-    unsigned long long* flag[2];   // peer arena address of the flag to publish
-    long long n16[2];         // payload size in 16-byte units
-};
-
-__global__ void __launch_bounds__(256) k_p2p_put(const CgScal* S, P2pPut d, unsigned long long seq, unsigned int* ticket) {
-    INK_PDL();
-    if (S->done) return;
-    for (int b = 0; b < 2; ++b) {
-        if (!d.src[b]) continue;
-        const uint4* __restrict__ s = reinterpret_cast<const uint4*>(d.src[b]);
-        uint4* __restrict__ t = reinterpret_cast<uint4*>(d.dst[b]);
-        for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < d.n16[b]; q += (long long)gridDim.x * blockDim.x) t[q] = s[q];
-    }
-    __threadfence_system();
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        const unsigned int tk = atomicAdd(ticket, 1u);
-        if (tk == gridDim.x - 1) {          // every block's stores are fenced: publish
-            *ticket = 0;
-            __threadfence_system();
-            for (int b = 0; b < 2; ++b)
-                if (d.src[b]) *reinterpret_cast<volatile unsigned long long*>(d.flag[b]) = seq;
-        }
-    }
-}
-
-// ---- wait for both neighbours' bands of sequence `seq`, optionally unpack them into their rows ------------------------
-struct P2pGet {
-    const unsigned long long* flag[2];   // LOCAL flags (nullptr = no neighbour on that side)
-    const void* src[2];                  // local arena payload
-    void* dst[2];                        // where to unpack (nullptr = leave in the arena)
-    long long n16[2];
-};
-
-__global__ void __launch_bounds__(256) k_p2p_wait_unpack(const CgScal* S, P2pGet d, unsigned long long seq) {
-    INK_PDL();
-    if (S->done) return;
-    if (threadIdx.x == 0)
-        for (int b = 0; b < 2; ++b)
-            if (d.flag[b]) p2p_spin(reinterpret_cast<const volatile unsigned long long*>(d.flag[b]), seq);
-    __syncthreads();
-    for (int b = 0; b < 2; ++b) {
-        if (!d.flag[b] || !d.dst[b]) continue;
-        const uint4* s = reinterpret_cast<const uint4*>(d.src[b]);
-        uint4* t = reinterpret_cast<uint4*>(d.dst[b]);
-        for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < d.n16[b]; q += (long long)gridDim.x * blockDim.x) {
-            uint4 v;
-            asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(s + q));   // L2: the peer wrote it
-            t[q] = v;
-        }
-    }
-}
+// ---- boundary bands ------------------------------------------------------------------------------------------------------
+// There are no stand-alone put / wait kernels: the PRODUCER of a band stores it a second time into the neighbour's arena
+// and its last block publishes the sequence number (P2pPush in cg.cuh: k_cg_init / k_cg_update for r; k_band_restore_weight
+// in mg_vec.cuh for the weighted z), and the CONSUMER kernel spins on its local flag before it reads the arena
+// (k_band_scale, k_band_combine).  The separate k_p2p_put + k_p2p_wait_unpack pair of the first version cost two launches
+// per exchange on the critical path (2 GPUs: 3.64 -> 2.99 ms per step when they were fused away).
 
 }  // namespace ink
