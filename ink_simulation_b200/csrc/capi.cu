@@ -915,7 +915,9 @@ struct Ctx final : CtxBase {
     int forces_impl(Real dt, int ext = 0) {
         if (int rc = ensure_seed()) return rc;
         const Real gx = dt * C.g[0], gy = dt * C.g[1], gz = dt * C.g[2];
-        { const Grid q = slab(ext); LAUNCH((k_dilate_add_gravity<Real>), cell_blocks(q), 256, q, C.R, seed, mark, gx, gy, gz, U(0), U(1), U(2)); }
+        { const Grid q = slab(ext);
+          if (vec4() && C.R <= 4) LAUNCH((k_dilate_add_gravity_v4<Real>), vec_blocks(q), 256, q, C.R, seed, mark, gx, gy, gz, U(0), U(1), U(2));
+          else LAUNCH((k_dilate_add_gravity<Real>), cell_blocks(q), 256, q, C.R, seed, mark, gx, gy, gz, U(0), U(1), U(2)); }
         CK(cudaGetLastError());
         if (oob_now) { phantom_v[0] += gx; phantom_v[1] += gy; phantom_v[2] += gz; }
         maxv_valid = false;

@@ -58,6 +58,65 @@ __device__ __forceinline__ Nbr4<Real> nbr4(const Real* __restrict__ f, const Gri
     return n;
 }
 
+// ------------------------------------------------------------------------------------------------
+// K2b  k_dilate_add_gravity for 4 z-consecutive cells per thread (System::applyExternalForces, src/waterSolver.cpp:158-191; Q8).
+// The scalar kernel walks the clipped Manhattan ball byte by byte (up to 63 one-byte loads per cell, two 64-bit divisions
+// for the decode); here a seed row contributes through at most three aligned 32-bit words: each word becomes a 4-bit
+// "non-zero byte" nibble, the three nibbles form a 12-bit window (cells k-4 .. k+7), the dilation along z by the row's
+// remaining radius is shifts and ORs, and bits 4..7 are this thread's cells.  Rows are visited ring by ring from the
+// centre, so inside a particle cloud the first row settles all four cells.  The mask is an OR over the same set of seed
+// bytes as the scalar kernel's, and a marked cell receives the same single addition: results are bit-identical.
+// Valid for R <= 4 (a window of +-4 cells around 4 cells is exactly the 12 bits).
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned int nz_nibble(uint32_t x) {   // bit b = (byte b of x != 0)
+    const uint32_t f = (((x & 0x7f7f7f7fu) + 0x7f7f7f7fu) | x) & 0x80808080u;
+    return ((f >> 7) | (f >> 14) | (f >> 21) | (f >> 28)) & 0xFu;
+}
+template <class Real>
+__device__ __forceinline__ void add_marked4(Real* __restrict__ p, Real gv, unsigned int m) {
+    V4<Real> q = ldp<Real, 4>(p);
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+        if ((m >> a) & 1u) q.a[a] += gv;
+    stp<Real, 4>(p, q);
+}
+template <class Real>
+__global__ void __launch_bounds__(256) k_dilate_add_gravity_v4(Grid g, int R, const uint8_t* __restrict__ seed, uint8_t* __restrict__ mark,
+                                                               Real gx, Real gy, Real gz, Real* __restrict__ u, Real* __restrict__ v, Real* __restrict__ w) {
+    INK_PDL();
+    int i, j, k; long long c;
+    if (!vec_cell_of_thread(g, blockIdx.x * blockDim.x + threadIdx.x, i, j, k, c)) return;
+    const bool zl = k > 0, zr = k + 4 < g.Z;
+    unsigned int acc = 0;
+    for (int ring = 0; ring <= R && acc != 0xFu; ++ring) {       // all (di, dj) with |di| + |dj| == ring
+        const int rk = R - ring;                                  // radius left for z
+        for (int dj = -ring; dj <= ring && acc != 0xFu; ++dj) {
+            const int jj = j + dj;
+            if (jj < 0 || jj >= g.Y) continue;
+            const int a = ring - abs(dj);
+            for (int s = 0; s < (a ? 2 : 1); ++s) {               // di = -a, +a
+                const int ii = i + (s ? a : -a);
+                if (ii < 0 || ii >= g.X) continue;
+                const uint32_t* __restrict__ row = reinterpret_cast<const uint32_t*>(seed + ((long long)jj * g.sy + (long long)ii * g.sx + k));
+                unsigned int m12 = nz_nibble(__ldg(row)) << 4;
+                if (rk > 0) {
+                    if (zl) m12 |= nz_nibble(__ldg(row - 1));
+                    if (zr) m12 |= nz_nibble(__ldg(row + 1)) << 8;
+                }
+                unsigned int d = m12;
+                for (int r = 1; r <= rk; ++r) d |= (m12 << r) | (m12 >> r);
+                acc |= (d >> 4) & 0xFu;
+            }
+        }
+    }
+    *reinterpret_cast<uint32_t*>(mark + c) = (acc & 1u) | ((acc & 2u) << 7) | ((acc & 4u) << 14) | ((acc & 8u) << 21);
+    if (acc) {
+        if (gx != Real(0)) add_marked4<Real>(u + c, gx, acc);   // adding an exact zero cannot change a value the reference would keep
+        if (gy != Real(0)) add_marked4<Real>(v + c, gy, acc);
+        if (gz != Real(0)) add_marked4<Real>(w + c, gz, acc);
+    }
+}
+
 // K3 (k_viscosity): l = ((((((0 + xp) + xm) + yp) + ym) + zp) + zm) - 6 f;  out = f + s l
 template <class Real>
 __device__ __forceinline__ V4<Real> visc4(const Real* __restrict__ f, const Grid& g, Real s, int i, int j, int k, long long c) {
