@@ -281,3 +281,29 @@ def test_gpu_two_systems_of_different_size_in_one_process():
     assert np.array_equal(np.stack(A.get_velocity()), np.stack(ref.get_velocity()))
     for T in (A, B, ref):
         T.close()
+
+
+def test_gpu_zero_rhs_after_a_developed_solve():
+    """Steady-state solves do not wait for the initial residual on the host (one sync less per step); the f == 0 special
+    case (solution exactly 0, whatever the warm start holds) is then recognised at the first poll.  A System with solver
+    history must give the same answer as a fresh one."""
+    dims = util.C2
+    A, B = gpu(dims), gpu(dims)
+    u, v, w = util.rand_field(dims, 31, scale=0.5)
+    A.set_velocity(u, v, w)
+    for _ in range(3):
+        A.pressure(0.17)                      # builds history: iteration count > 1, non-zero warm start
+    assert A.stats().cg_iters > 1
+    zero = [np.zeros(dims, np.float32)] * 3
+    for T in (A, B):
+        T.set_velocity(*zero)
+        T.pressure(0.17)
+    assert A.stats().cg_iters == 0 and B.stats().cg_iters == 0
+    assert np.array_equal(A.get_pressure(), B.get_pressure()) and np.array_equal(A.get_warm_start(), np.zeros(dims, np.float32))
+    assert np.array_equal(np.stack(A.get_velocity()), np.stack(B.get_velocity()))
+    # and the next non-trivial solve is unaffected by what the blind iterations left behind
+    for T in (A, B):
+        T.set_velocity(u, v, w)
+        T.pressure(0.17)
+    assert util.rel_inf(np.stack(A.get_velocity()), np.stack(B.get_velocity())) < 1e-5
+    A.close(); B.close()
