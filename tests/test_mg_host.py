@@ -80,3 +80,55 @@ def test_pcg_iteration_count_with_host_vcycle(harness):
     x, it = mg_proto.pcg(f, lambda r: apply_B(harness, r, prec=32))
     assert it <= 11
     assert np.linalg.norm(f - mg_proto.M(x)) <= 2e-6 * np.linalg.norm(f)
+
+
+def schwarz_weights(Y, world, rank):
+    """sqrt of the linear partition of unity of capi.cu: mg_setup (weighted overlapping Schwarz)."""
+    lo = [Y * r // world for r in range(world + 1)]
+    ovl = max(1, min(8, min(lo[r + 1] - lo[r] for r in range(world)) // 2))
+    j0, j1 = lo[rank], lo[rank + 1]
+    je0, je1 = (j0 - ovl if rank > 0 else j0), (j1 + ovl if rank + 1 < world else j1)
+    w = np.zeros(Y)
+    for j in range(je0, je1):
+        v = 1.0
+        if rank > 0 and j < j0 + ovl:
+            v = min(v, (j - (j0 - ovl) + 0.5) / (2.0 * ovl))
+        if rank + 1 < world and j >= j1 - ovl:
+            v = min(v, ((j1 + ovl) - j - 0.5) / (2.0 * ovl))
+        w[j] = v
+    return je0, je1, w
+
+
+def schwarz_B(exe, r, world):
+    """z = sum_i sqrt(W_i) B_i sqrt(W_i) r: what k_band_scale -> slab-local V-cycle -> k_band_restore_weight -> k_band_combine
+    compute together on `world` GPUs, here with the slab-local V-cycles run on the host one after the other."""
+    z = np.zeros_like(r)
+    for rank in range(world):
+        je0, je1, w = schwarz_weights(r.shape[1], world, rank)
+        sw = np.sqrt(w)[None, :, None]
+        z += sw * apply_B(exe, sw * r, je0, je1)
+    return z
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_weighted_schwarz_preconditioner_at_2_4_8_ranks(harness, world):
+    """The distributed preconditioner as an operator: partition of unity, symmetric, positive definite, and PCG with it
+    needs no more than one iteration above the single-slab V-cycle (measured on B200: 12.1 / 12.5 / 12.4 against 11.5)."""
+    import mg_proto
+
+    shape = (12, 16 * world, 12)
+    Y = shape[1]
+    tot = sum(schwarz_weights(Y, world, r)[2] for r in range(world))
+    assert np.allclose(tot, 1.0, atol=1e-15)                                    # the weights are a partition of unity on every row
+    rng = np.random.default_rng(3)
+    x, y = rng.standard_normal(shape), rng.standard_normal(shape)
+    Bx, By = schwarz_B(harness, x, world), schwarz_B(harness, y, world)
+    a, b = float(np.vdot(Bx, y)), float(np.vdot(x, By))
+    assert abs(a - b) <= 1e-12 * max(abs(a), abs(b))
+    assert float(np.vdot(Bx, x)) > 0 and float(np.vdot(By, y)) > 0
+    u = rng.standard_normal((3,) + shape)
+    f = np.diff(u[0], axis=0, append=0) + np.diff(u[1], axis=1, append=0) + np.diff(u[2], axis=2, append=0)
+    _, it1 = mg_proto.pcg(f, lambda r: apply_B(harness, r))
+    xs, itw = mg_proto.pcg(f, lambda r: schwarz_B(harness, r, world))
+    assert itw <= it1 + 1, (itw, it1)
+    assert np.linalg.norm(f - mg_proto.M(xs)) <= 2e-6 * np.linalg.norm(f)
