@@ -156,3 +156,75 @@ def test_gpu_cpp_binary_checkpoint_resume_and_cross_host(tmp_path):
     P.simulate(float(np.float32(0.05)), n2)
     assert filecmp.cmpfiles(os.path.join(a, "drop0"), os.path.join(c, "drop0"), frames, shallow=False)[0] == frames
     assert filecmp.cmp(os.path.join(a, "velocityField.ply"), os.path.join(c, "velocityField.ply"), shallow=False)
+
+
+# ---------------------------------------------------------------------------------------------------------------------------
+class FakeSystem:
+    """Stands in for System on a CPU-only machine: deterministic state that depends on every solve() so far, and the
+    accessors InkSim uses.  Lets the run loop, frame pacing and checkpoint bookkeeping of inksim.py be tested without a GPU."""
+
+    class _P:
+        cell_dim = 1.0
+
+    def __init__(self, dims=(3, 4, 2), n=5):
+        self.dims, self.params = dims, self._P()
+        self.pos = np.arange(3 * n, dtype=np.float32).reshape(n, 3)
+        self.vel = np.zeros((n, 3), np.float32)
+        self.u = [np.full(dims, a, np.float32) for a in (1, 2, 3)]
+        self.q = np.zeros(dims, np.float32)
+        self.asked = []
+
+    def solve(self, ttnr):
+        self.asked.append(ttnr)
+        dt = min(ttnr, 0.02 + 0.013 * (int(self.pos[0, 0] * 1000) % 3))   # a function of the STATE only (as in the real solver):
+        # sometimes the CFL step, sometimes the time to the next frame
+        self.pos = (self.pos + np.float32(dt)).astype(np.float32)
+        self.vel = (self.vel * np.float32(0.5) + np.float32(dt)).astype(np.float32)
+        self.u = [(a * np.float32(1.01) + np.float32(dt)).astype(np.float32) for a in self.u]
+        self.q = (self.q + self.u[0] * np.float32(1e-3)).astype(np.float32)
+        return dt
+
+    def num_drops(self): return 1
+    def get_particles(self, d=0): return self.pos.copy(), self.vel.copy()
+    def get_velocity(self): return [a.copy() for a in self.u]
+    def get_warm_start(self): return self.q.copy()
+    def set_velocity(self, u, v, w): self.u = [np.array(a, np.float32) for a in (u, v, w)]
+    def set_warm_start(self, q): self.q = np.array(q, np.float32)
+    def set_particles(self, pos, vel=None, drop=0): self.pos, self.vel = np.array(pos, np.float32), np.array(vel, np.float32)
+
+
+def tree(root):
+    out = {}
+    for d, _, files in os.walk(root):
+        for f in files:
+            if "checkpoint" not in d:
+                out[os.path.relpath(os.path.join(d, f), root)] = open(os.path.join(d, f), "rb").read()
+    return out
+
+
+def test_run_loop_pacing_and_checkpoint_bookkeeping_without_a_gpu(tmp_path):
+    render, n1, n2 = 0.05, 11, 9
+    a = inksim.InkSim(tmp_path / "a", FakeSystem())
+    a.simulate(render, n1 + n2)
+    # pacing of src/inkSim.cpp:17-31 in float arithmetic: solve() is asked for the time left to the next frame, a frame is
+    # written when the accumulated time reaches renderTimestep, numbering starts at 1
+    asked = a.ink_system.asked
+    assert asked[0] == float(np.float32(render)) and all(0 < t <= asked[0] for t in asked)
+    frames = sorted(int(f.split(".")[0]) for f in os.listdir(tmp_path / "a" / "drop0"))
+    assert frames == list(range(1, len(frames) + 1)) and 3 < len(frames) < n1 + n2
+    b = inksim.InkSim(tmp_path / "b", FakeSystem())
+    b.simulate(render, n1)
+    b.writeCheckpoint()
+    meta = open(tmp_path / "b" / "checkpoint" / "meta.txt").read().split()
+    assert meta[:4] == ["grid", "3", "4", "2"] and meta[4:6] == ["drops", "1"] and meta[6] == "next_frame" and meta[8] == "time_since_last_render_bits"
+    c = inksim.InkSim(tmp_path / "b", FakeSystem())          # fresh object, fresh "device" state
+    assert c.resume()
+    assert np.array_equal(c.ink_system.pos, b.ink_system.pos) and np.array_equal(c.ink_system.q, b.ink_system.q)
+    c.simulate(render, n2)
+    assert tree(tmp_path / "a") == tree(tmp_path / "b")      # every frame and velocityField.ply, byte for byte
+    assert c.ink_system.asked == asked[n1:]                  # the resumed run asked solve() for exactly the same times
+    # a plain second simulate() starts again at frame 1, like the reference; a checkpoint of another grid is refused
+    c.simulate(render, 3)
+    assert c.ink_system.asked[n2] == float(np.float32(render))
+    with pytest.raises(ValueError):
+        inksim.InkSim(tmp_path / "b", FakeSystem(dims=(3, 4, 3))).resume()
