@@ -313,6 +313,14 @@ def main():
     from ink_simulation_b200 import System
 
     torch.cuda.set_device(local)
+    # One process per GPU: keep this rank's pinned staging buffers and copy-issuing thread on the GPU's own NUMA node (every
+    # step moves 120 MB each way per GPU; round 1 measured the e2e of 8 unbound ranks at ~100 GB/s for the whole box).
+    # N = 1 is left alone: the cpu_baseline leg uses all host cores.  INK_NO_AFFINITY=1 switches it off for A/B runs.
+    host_affinity = "unchanged (single process)"
+    if world > 1 and not os.environ.get("INK_NO_AFFINITY"):
+        from ink_simulation_b200 import bind_host_to_gpu
+
+        host_affinity = bind_host_to_gpu(local)
     if world > 1:
         import torch.distributed as dist
 
@@ -513,7 +521,7 @@ def main():
         "warmup": max(3, args.warmup), "ms_per_step": ms_step, "higher_is_better": True,
         "scaling": "strong" if (world > 1 and args.strong) else "weak", "vs_baseline": None,
         "dtype": args.dtype, "data": "synthetic",
-        "config": workload_config(args, cfg, dims, n, world),
+        "config": dict(workload_config(args, cfg, dims, n, world), host_affinity=host_affinity),
         "mac_cell_steps_per_s": ncell / (ms_step * 1e-3),
         "mac_only_cell_steps_per_s": ncell / (water_ms * 1e-3) if water_ms > 0 else None,
         "particles_only_updates_per_s": n / (part_ms * 1e-3) if part_ms > 0 else None,

@@ -7,5 +7,5 @@ Layout:  csrc/  CUDA kernels + the C ABI (include/ink_capi.h -> libinkb200.so)
                 checkpoints, the reference's seeders) for tests and bench.py
 """
 from ._capi import LIB_PATH, load  # noqa: F401
-from .system import InkError, Params, System, create_distributed, nccl_unique_id, shard_range, slab_range  # noqa: F401
+from .system import InkError, Params, System, bind_host_to_gpu, create_distributed, nccl_unique_id, shard_range, slab_range  # noqa: F401
 from .inksim import InkSim  # noqa: F401,E402

@@ -7,6 +7,7 @@ the same against all three).  All compute happens in libinkb200.so on the GPU; t
 from __future__ import annotations
 
 import ctypes as C
+import os
 from dataclasses import dataclass
 
 import numpy as np
@@ -61,6 +62,43 @@ def shard_range(n, rank, world_size):
 def slab_range(Y, rank, world_size):
     """Grid rows [j0, j1) that `rank` owns (same rule as ink_create)."""
     return Y * rank // world_size, Y * (rank + 1) // world_size
+
+
+def bind_host_to_gpu(device=0):
+    """Restrict the calling process to the CPUs NVML reports as local to CUDA device `device`, so that pinned staging buffers
+    allocated afterwards (first touch) and the copy-issuing thread sit on that GPU's NUMA node.  With one process per GPU and
+    120 MB of positions each way per step and per GPU (bench.py e2e, the .ply frame path), host buffers on the wrong socket
+    send every byte across the inter-socket link: 8 ranks then share ~100 GB/s instead of having a PCIe link each.
+    Purely a placement hint: any failure (no NVML, container cpuset that excludes those CPUs, single NUMA node) leaves the
+    process as it was.  Returns a one-line description of what was done."""
+    try:
+        import pynvml
+
+        pynvml.nvmlInit()
+        handle = None
+        try:
+            import torch
+
+            uuid = str(torch.cuda.get_device_properties(device).uuid)
+            handle = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
+        except Exception:
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+            ids = [v for v in vis.split(",") if v.strip()]
+            idx = int(ids[device]) if ids and all(v.strip().isdigit() for v in ids) and device < len(ids) else device
+            handle = pynvml.nvmlDeviceGetHandleByIndex(idx)
+        ncpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(handle, (ncpu + 63) // 64)
+        local = {64 * w + b for w, m in enumerate(words) for b in range(64) if (int(m) >> b) & 1}
+        allowed = os.sched_getaffinity(0)
+        target = local & allowed
+        if not target:
+            return "unchanged (the GPU's local CPUs are outside this process's cpuset)"
+        if target == allowed:
+            return f"unchanged (all {len(allowed)} allowed CPUs are local to the GPU)"
+        os.sched_setaffinity(0, target)
+        return f"bound to the {len(target)} CPUs local to GPU {device} (of {len(allowed)} allowed)"
+    except Exception as e:  # noqa: BLE001 - a hint must never take the run down
+        return f"unchanged ({type(e).__name__})"
 
 
 def create_distributed(X, Y, Z, **kw):

@@ -66,3 +66,34 @@ def test_sharding_rules_on_two_gloo_ranks(tmp_path):
            "--master-port", "29534", str(script)]
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
     assert out.returncode == 0 and out.stdout.count("GLOO-OK") == 2, out.stdout[-2000:] + out.stderr[-2000:]
+
+
+def test_bind_host_to_gpu_is_a_safe_hint(monkeypatch):
+    """bench.py calls bind_host_to_gpu(LOCAL_RANK) under torchrun so that each rank's pinned buffers sit on its GPU's NUMA
+    node.  It must never raise, must only ever SHRINK the affinity to CPUs the process already has, and must do nothing when
+    NVML is missing or its answer is useless."""
+    import types
+
+    from ink_simulation_b200 import bind_host_to_gpu
+
+    before = os.sched_getaffinity(0)
+    try:
+        monkeypatch.setitem(sys.modules, "pynvml", None)                 # import fails
+        assert bind_host_to_gpu(0).startswith("unchanged") and os.sched_getaffinity(0) == before
+        fake = types.ModuleType("pynvml")
+        fake.nvmlInit = lambda: None
+        fake.nvmlDeviceGetHandleByUUID = lambda u: (_ for _ in ()).throw(RuntimeError("no such uuid"))
+        fake.nvmlDeviceGetHandleByIndex = lambda i: ("handle", i)
+        monkeypatch.setitem(sys.modules, "pynvml", fake)
+        mask_all = sum(1 << c for c in before)
+        fake.nvmlDeviceGetCpuAffinity = lambda h, n: [(mask_all >> (64 * w)) & (2**64 - 1) for w in range(n)]
+        assert bind_host_to_gpu(0).startswith("unchanged") and os.sched_getaffinity(0) == before      # everything is local already
+        fake.nvmlDeviceGetCpuAffinity = lambda h, n: [0] * n
+        assert bind_host_to_gpu(0).startswith("unchanged") and os.sched_getaffinity(0) == before      # empty intersection
+        if len(before) >= 2:
+            keep = sorted(before)[: len(before) // 2]
+            sub = sum(1 << c for c in keep) | (1 << (max(before) + 7))                                 # plus a CPU we do not own
+            fake.nvmlDeviceGetCpuAffinity = lambda h, n: [(sub >> (64 * w)) & (2**64 - 1) for w in range(n)]
+            assert bind_host_to_gpu(0).startswith("bound to the") and os.sched_getaffinity(0) == set(keep)
+    finally:
+        os.sched_setaffinity(0, before)
