@@ -4,7 +4,8 @@
 // render.py's reader does not look at) followed by raw host-endian fp32 records in particle index order.
 // Differences, all on the I/O side: the drop<i>/ directories are created (the reference leaves that to the user and
 // silently writes nothing otherwise, :49-51); a frame is ONE write() of a pinned buffer filled by one D2H copy instead
-// of 3 ofstream::write calls per particle; the write overlaps the next solver steps; velocityField.ply holds exactly
+// of 3 ofstream::write calls per particle; both the copy (library copy stream, ink_fetch_positions_async) and the write (a
+// writer thread) overlap the next solver steps; velocityField.ply holds exactly
 // X*Y*Z records in i-j-k order (the reference dumps its hash map in bucket order, phantom cells included — SURVEY Q17).
 #include "inkSim.h"
 
@@ -19,6 +20,8 @@
 
 #include <cuda_runtime_api.h>
 
+static void write_blob(const std::string& filename, const std::string& header, const float* data, size_t floats);
+
 InkSim::InkSim(std::string writeDirectory) {
     this->ink_system.init();
     this->ink_system.checkNanAndInf();
@@ -26,12 +29,28 @@ InkSim::InkSim(std::string writeDirectory) {
 }
 
 InkSim::~InkSim() {
-    drain();
+    try { drain(); } catch (const std::exception& e) { std::cerr << "InkSim: " << e.what() << std::endl; }   // never throw from a destructor
     for (auto& b : m_buf)
         if (b.host) cudaFreeHost(b.host);
 }
 
+void InkSim::flushPending() {
+    bool any = false;
+    for (auto& b : m_buf) any = any || b.pending;
+    if (!any) return;
+    ink_system.syncIO();   // every enqueued device-to-host copy has landed
+    for (auto& b : m_buf) {
+        if (!b.pending) continue;
+        b.pending = false;
+        float* host = b.host;
+        b.writer = std::thread([host, off = b.off, names = b.names, headers = b.headers]() {
+            for (size_t i = 0; i + 1 < off.size(); i++) write_blob(names[i], headers[i], host + off[i], off[i + 1] - off[i]);
+        });
+    }
+}
+
 void InkSim::drain() {
+    flushPending();
     for (auto& b : m_buf)
         if (b.writer.joinable()) b.writer.join();
 }
@@ -100,27 +119,28 @@ extern "C" void inkhost_write_particles_ply(const char* filename, const float* x
 }
 
 void InkSim::writeToFile(int frameNum) {
+    flushPending();   // the previous frame's copy has had the steps in between to complete; its file write starts now
     const int drops = ink_system.numDrops();
     size_t total = 0;
     std::vector<size_t> off(drops + 1, 0);
     for (int i = 0; i < drops; i++) { total += (size_t)ink_system.numParticles(i) * 3; off[i + 1] = total; }
     FrameBuf& b = m_buf[m_cur];
     m_cur ^= 1;
-    float* host = stage(b, total);
-    std::vector<std::string> names(drops), headers(drops);
+    float* host = stage(b, total);   // waits until the frame before the previous one is on disk: its buffer is reused
+    b.off = off;
+    b.names.assign(drops, "");
+    b.headers.assign(drops, "");
     for (int i = 0; i < drops; i++) {
         std::string path = this->writeDirectory + "/drop" + std::to_string(i);
         std::filesystem::create_directories(path);
-        names[i] = path + "/" + std::to_string(frameNum) + ".ply";
-        std::cout << "writing to: " + names[i] << std::endl;
+        b.names[i] = path + "/" + std::to_string(frameNum) + ".ply";
+        std::cout << "writing to: " + b.names[i] << std::endl;
         std::string numVertices = std::to_string(ink_system.numParticles(i));
         std::cout << "recording " + numVertices + " particles" << std::endl;
-        headers[i] = particle_ply_header(ink_system.numParticles(i));
-        ink_system.copyPositions(i, host + off[i]);   // D2H into pinned memory, original particle order
+        b.headers[i] = particle_ply_header(ink_system.numParticles(i));
+        ink_system.fetchPositionsAsync(i, host + off[i]);   // snapshot in stream order, D2H on the copy stream, original particle order
     }
-    b.writer = std::thread([host, off, names, headers, drops]() {
-        for (int i = 0; i < drops; i++) write_blob(names[i], headers[i], host + off[i], off[i + 1] - off[i]);
-    });
+    b.pending = true;
 }
 
 // header of a dump with `props` float properties per record; the first three are always x y z

@@ -33,7 +33,13 @@ private:
 
     // asynchronous frame output: positions land in one of two pinned host buffers, a writer thread streams the
     // previous frame to disk while the GPU already computes the next steps
-    struct FrameBuf { float* host = nullptr; size_t cap = 0; std::thread writer; };
+    // — and the device-to-host copy of a frame runs on the library's copy stream while the next steps compute: a frame's
+    // copy is only waited for (and its file write started) when the NEXT frame is due, at a checkpoint or at the end
+    struct FrameBuf {
+        float* host = nullptr; size_t cap = 0; std::thread writer;
+        bool pending = false;                       // copy enqueued, file write not started yet
+        std::vector<size_t> off; std::vector<std::string> names, headers;
+    };
     // frame pacing carried across simulate() calls only through resume(): like the reference, a plain second call to
     // simulate() starts again at frame 1
     int m_nextFrame = 1;
@@ -43,7 +49,8 @@ private:
     FrameBuf m_buf[2];
     int m_cur = 0;
     float* stage(FrameBuf& b, size_t floats);
-    void drain();
+    void flushPending();                            // wait for enqueued copies, hand their frames to writer threads
+    void drain();                                   // flushPending + wait for every file to be on disk
 };
 
 #endif  // INK_SIM_H

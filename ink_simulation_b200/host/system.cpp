@@ -84,6 +84,12 @@ long long System::numParticles(int drop) const { return ink_num_particles(m_ctx,
 void System::copyPositions(int drop, float* xyz) {
     if (ink_get_particles(m_ctx, drop, xyz, nullptr, 32) != 0) fail("ink_get_particles");
 }
+void System::fetchPositionsAsync(int drop, float* xyz) {
+    if (ink_fetch_positions_async(m_ctx, drop, xyz, 32) != 0) fail("ink_fetch_positions_async");
+}
+void System::syncIO() {
+    if (ink_sync_io(m_ctx) != 0) fail("ink_sync_io");
+}
 void System::copyVelocityField(float* u, float* v, float* w) {
     if (ink_get_field(m_ctx, INK_FIELD_CURR, u, v, w, 32) != 0) fail("ink_get_field");
 }

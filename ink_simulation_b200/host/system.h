@@ -116,6 +116,10 @@ public:
     int numDrops() const;
     long long numParticles(int drop) const;
     void copyPositions(int drop, float* xyz);
+    // same, asynchronously (ink_fetch_positions_async): returns at once, `xyz` (pinned host memory) is complete after
+    // syncIO(); the device snapshot is taken in stream order, so later solve() calls do not disturb it
+    void fetchPositionsAsync(int drop, float* xyz);
+    void syncIO();
     // dense currVelocity, (X, Y, Z) C-order, three arrays of X*Y*Z floats
     void copyVelocityField(float* u, float* v, float* w);
     ink_ctx* handle() { return m_ctx; }
