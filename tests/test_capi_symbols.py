@@ -84,3 +84,12 @@ def test_product_does_not_import_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h")):
                 txt = open(os.path.join(base, f)).read()
                 assert "import oracle" not in txt and "libinkoracle" not in txt and "libinkref" not in txt, f
+
+
+def test_every_entry_point_is_mapped_to_the_reference_in_the_docs():
+    """INTEGRATION.md is what a maintainer of the reference binds against: every entry point of the header must appear there
+    (with the reference member it replaces, or 'no reference equivalent'), and the header itself must cite reference lines."""
+    doc = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    missing = [n for n in declared_symbols() if n not in doc]
+    assert not missing, missing
+    assert len(re.findall(r"src/[A-Za-z]+\.(?:cpp|h):\d+", open(HEADER).read())) >= 15
