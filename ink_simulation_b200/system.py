@@ -95,6 +95,8 @@ def bind_host_to_gpu(device=0):
             return "unchanged (the GPU's local CPUs are outside this process's cpuset)"
         if target == allowed:
             return f"unchanged (all {len(allowed)} allowed CPUs are local to the GPU)"
+        if len(target) < 4:   # NCCL's proxy and torch's helper threads inherit the mask: never squeeze a rank onto a couple of cores
+            return f"unchanged (only {len(target)} of the allowed CPUs are local to the GPU)"
         os.sched_setaffinity(0, target)
         return f"bound to the {len(target)} CPUs local to GPU {device} (of {len(allowed)} allowed)"
     except Exception as e:  # noqa: BLE001 - a hint must never take the run down

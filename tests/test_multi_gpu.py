@@ -90,7 +90,10 @@ def test_bind_host_to_gpu_is_a_safe_hint(monkeypatch):
         assert bind_host_to_gpu(0).startswith("unchanged") and os.sched_getaffinity(0) == before      # everything is local already
         fake.nvmlDeviceGetCpuAffinity = lambda h, n: [0] * n
         assert bind_host_to_gpu(0).startswith("unchanged") and os.sched_getaffinity(0) == before      # empty intersection
-        if len(before) >= 2:
+        one = 1 << min(before)
+        fake.nvmlDeviceGetCpuAffinity = lambda h, n: [(one >> (64 * w)) & (2**64 - 1) for w in range(n)]
+        assert bind_host_to_gpu(0).startswith("unchanged") and os.sched_getaffinity(0) == before      # would squeeze the rank onto 1 core
+        if len(before) >= 8:
             keep = sorted(before)[: len(before) // 2]
             sub = sum(1 << c for c in keep) | (1 << (max(before) + 7))                                 # plus a CPU we do not own
             fake.nvmlDeviceGetCpuAffinity = lambda h, n: [(sub >> (64 * w)) & (2**64 - 1) for w in range(n)]
