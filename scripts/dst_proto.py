@@ -1,0 +1,80 @@
+"""Prototype of the fast-Poisson preconditioner (git branch r2-dst, csrc/dst.cuh): the pressure operator M = -A is exactly
+diagonalised by three orthonormal type-I sine transforms, applied as DENSE matrices (GEMMs) because the FFT sizes would be
+2(n+1) = 258 / 514.  Two questions, answered on the CPU:
+
+1. Is one fp32 application accurate enough?            python scripts/dst_proto.py accuracy
+   (128, 256, 128): fp32 relative residual 6.8e-07 (CG tolerance 1e-6), max error vs the exact solution 1.4e-06
+   (the reference's own fp32 SparseLU is 4e-06 away), 3.3e-08 after one refinement step.
+2. How many PCG iterations with exact slab solves inside the weighted overlapping Schwarz preconditioner (multi-GPU)?
+                                                        python scripts/dst_proto.py schwarz
+   (64, 256, 64): 1 rank 1 iteration; 2 ranks 5; 4 ranks 6; 8 ranks 6   (trilinear V-cycle today: 11.5 / 12.1 / 12.5 / 12.4)
+"""
+import os
+import sys
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
+import mg_proto as P  # noqa: E402
+
+
+def S(n, dt=np.float64):
+    a = np.arange(1, n + 1)
+    return (np.sin(np.pi * np.outer(a, a) / (n + 1)) * np.sqrt(2.0 / (n + 1))).astype(dt)
+
+
+def lam1(n):
+    return 2 - 2 * np.cos(np.pi * np.arange(1, n + 1) / (n + 1))
+
+
+def dst_solve(f, dt=np.float64):
+    X, Y, Z = f.shape
+    Sx, Sy, Sz = S(X, dt), S(Y, dt), S(Z, dt)
+    g = f.astype(dt)
+    g = np.einsum("ck,abk->abc", Sz, g, optimize=True).astype(dt)
+    g = np.einsum("ai,ijk->ajk", Sx, g, optimize=True).astype(dt)
+    g = np.einsum("bj,ajk->abk", Sy, g, optimize=True).astype(dt)
+    g = (g / (lam1(X)[:, None, None] + lam1(Y)[None, :, None] + lam1(Z)[None, None, :]).astype(dt)).astype(dt)
+    g = np.einsum("bj,ajk->abk", Sy, g, optimize=True).astype(dt)
+    g = np.einsum("ai,ijk->ajk", Sx, g, optimize=True).astype(dt)
+    g = np.einsum("ck,abk->abc", Sz, g, optimize=True).astype(dt)
+    return g
+
+
+def rhs(shape):
+    u = np.random.default_rng(0).standard_normal((3,) + shape)
+    return np.diff(u[0], axis=0, append=0) + np.diff(u[1], axis=1, append=0) + np.diff(u[2], axis=2, append=0)
+
+
+def accuracy():
+    for shape in [(32, 64, 32), (64, 128, 64), (128, 256, 128)]:
+        f = rhs(shape)
+        q64, q32 = dst_solve(f, np.float64), dst_solve(f, np.float32)
+        res = lambda q: np.linalg.norm(f - P.M(q.astype(np.float64))) / np.linalg.norm(f)  # noqa: E731
+        r = (f - P.M(q32.astype(np.float64))).astype(np.float32)
+        q2 = q32 + dst_solve(r, np.float32)
+        print(shape, "fp64 residual %.1e | fp32 residual %.1e, max error vs exact %.1e | after one refinement %.1e"
+              % (res(q64), res(q32), np.abs(q32 - q64).max() / np.abs(q64).max(), res(q2)))
+
+
+def schwarz():
+    from test_mg_host import schwarz_weights
+
+    def B(r, world, dt):
+        z = np.zeros_like(r)
+        for rank in range(world):
+            je0, je1, w = schwarz_weights(r.shape[1], world, rank)
+            sw = np.sqrt(w)[None, :, None]
+            z[:, je0:je1] += sw[:, je0:je1] * dst_solve((sw * r)[:, je0:je1], dt)
+        return z
+
+    for shape in [(32, 128, 32), (64, 256, 64)]:
+        f = rhs(shape)
+        for world in (1, 2, 4, 8):
+            x, it = P.pcg(f, lambda r: B(r, world, np.float32).astype(np.float64), rtol=1e-6)
+            print(shape, "ranks", world, "PCG iterations", it, "true residual %.1e" % (np.linalg.norm(f - P.M(x)) / np.linalg.norm(f)))
+
+
+if __name__ == "__main__":
+    {"accuracy": accuracy, "schwarz": schwarz}[sys.argv[1] if len(sys.argv) > 1 else "accuracy"]()
