@@ -13,6 +13,13 @@ diagonalised by three orthonormal type-I sine transforms, applied as DENSE matri
    (128, 512, 128), 2 ranks: overlap 4 -> 8 iterations, 8 -> 6, 16 -> 4, 32 -> 2
    (128, 1024, 128), 4 ranks: overlap 4 -> 10, 8 -> 6, 16 -> 4, 32 -> 3
    With an exact block solve the count keeps falling with the overlap (it does not with the V-cycle): 32 rows it is.
+4. Which tensor-core arithmetic would do for the six GEMMs (tcgen05 kind::tf32 / kind::f16, fp32 accumulation)?
+                                                        python scripts/dst_proto.py precision
+   (64, 128, 64), residual of one application | PCG iterations to 1e-6:
+     fp32 4.7e-07 | 1      tf32 7.5e-04 | 2      3 x tf32 (split operands) 4.9e-07 | 1
+     bf16 5.4e-03 | 3      3 x bf16 1.1e-05 | 2  6 x bf16 2.2e-07 | 1
+   A single-pass TF32 transform is a good enough PRECONDITIONER: two CG iterations, each six tensor-core GEMMs that are then
+   bound by their 48 B/cell of traffic, not by arithmetic.
 """
 import os
 import sys
@@ -81,6 +88,47 @@ def schwarz():
             print(shape, "ranks", world, "PCG iterations", it, "true residual %.1e" % (np.linalg.norm(f - P.M(x)) / np.linalg.norm(f)))
 
 
+def _round_mantissa(x, keep_bits):
+    u = np.ascontiguousarray(x, np.float32).view(np.uint32).copy()
+    drop = 23 - keep_bits
+    u = (u + np.uint32(1 << (drop - 1))) & np.uint32((0xFFFFFFFF >> drop) << drop)
+    return u.view(np.float32)
+
+
+def precision():
+    def mm(spec, Sm, g, mode):
+        Sm, g = Sm.astype(np.float32), g.astype(np.float32)
+        if mode == "fp32":
+            return np.einsum(spec, Sm, g, optimize=True).astype(np.float32)
+        rnd = (lambda x: _round_mantissa(x, 10)) if "tf32" in mode else (lambda x: _round_mantissa(x, 7))
+        Sh, gh = rnd(Sm), rnd(g)
+        out = np.einsum(spec, Sh, gh, optimize=True)
+        if "x" in mode:   # split operands: hi*hi + hi*lo + lo*hi (+ three more terms for "x6")
+            Sl, gl = rnd(Sm - Sh), rnd(g - gh)
+            out = out + np.einsum(spec, Sh, gl, optimize=True) + np.einsum(spec, Sl, gh, optimize=True)
+            if mode.endswith("x6"):
+                Sl2, gl2 = rnd(Sm - Sh - Sl), rnd(g - gh - gl)
+                out = out + np.einsum(spec, Sl, gl, optimize=True) + np.einsum(spec, Sh, gl2, optimize=True) + np.einsum(spec, Sl2, gh, optimize=True)
+        return out.astype(np.float32)
+
+    def solve(f, mode):
+        X, Y, Z = f.shape
+        Sx, Sy, Sz = S(X), S(Y), S(Z)
+        g = f.astype(np.float32)
+        g = mm("ck,abk->abc", Sz, g, mode); g = mm("ai,ijk->ajk", Sx, g, mode); g = mm("bj,ajk->abk", Sy, g, mode)  # noqa: E702
+        g = (g / (lam1(X)[:, None, None] + lam1(Y)[None, :, None] + lam1(Z)[None, None, :]).astype(np.float32)).astype(np.float32)
+        g = mm("bj,ajk->abk", Sy, g, mode); g = mm("ai,ijk->ajk", Sx, g, mode); g = mm("ck,abk->abc", Sz, g, mode)  # noqa: E702
+        return g
+
+    shape = (64, 128, 64)
+    f = rhs(shape)
+    for mode in ("fp32", "tf32", "tf32x3", "bf16", "bf16x3", "bf16x6"):
+        q = solve(f, mode)
+        res = np.linalg.norm(f - P.M(q.astype(np.float64))) / np.linalg.norm(f)
+        _, it = P.pcg(f, lambda r: solve(r, mode).astype(np.float64), rtol=1e-6)
+        print("%-7s one application: residual %.1e | PCG iterations to 1e-6: %d" % (mode, res, it))
+
+
 def overlap():
     def weights(Y, world, rank, ovl):
         lo = [Y * r // world for r in range(world + 1)]
@@ -112,4 +160,4 @@ def overlap():
 
 
 if __name__ == "__main__":
-    {"accuracy": accuracy, "schwarz": schwarz, "overlap": overlap}[sys.argv[1] if len(sys.argv) > 1 else "accuracy"]()
+    {"accuracy": accuracy, "schwarz": schwarz, "overlap": overlap, "precision": precision}[sys.argv[1] if len(sys.argv) > 1 else "accuracy"]()
