@@ -6,7 +6,12 @@
  * repo): every entry point names the reference member it replaces.  Plain pointers and sizes only;
  * no C++/Eigen/torch types cross the boundary.  All calls return 0 on success, non-zero on error
  * (message via ink_last_error).  One ctx = one host thread = one CUDA device; all work is ordered
- * on the ctx's stream.  There is NO CPU fallback: ink_create fails if no sm_100 device is present.
+ * on the ctx's OWN non-blocking CUDA stream (ink_get_stream), never the legacy NULL stream.  Consequences for DEVICE
+ * pointers: inputs must be complete before the call (the library's stream is not ordered against the caller's streams —
+ * synchronise, or make the ctx stream wait on your event via ink_get_stream); device outputs and the caller's input
+ * buffers are complete / free again when the call returns (the streaming calls ink_prefetch_positions /
+ * ink_fetch_positions_async are the documented exception: they return at once).  There is NO CPU fallback:
+ * ink_create fails if no sm_100 device is present.
  *
  * Array conventions (identical to oracle/ and the compiled-reference shim):
  *   grid fields  : dense (X, Y, Z) C-order, z fastest: idx = (i*Y + j)*Z + k
@@ -68,6 +73,8 @@ typedef struct ink_stats {
     int64_t steps;          /* ink_step calls so far */
     int64_t resorts;        /* particle re-binnings so far */
     int64_t kernel_launches;/* kernels launched by this ctx so far */
+    int32_t cg_converged;   /* 1: the last pressure solve met cg_rtol; 0: it stopped at cg_max_iters (ink_step then returns an error) */
+    int32_t graph_launches; /* CUDA-graph launches by this ctx so far (each replays one captured PCG iteration) */
 } ink_stats;
 
 void ink_default_params(ink_params* p);                 /* the committed values of src/system.h:13-38 */
@@ -133,6 +140,16 @@ int  ink_commit_positions(ink_ctx* c, int drop);
 int  ink_fetch_positions_async(ink_ctx* c, int drop, void* pos_xyz, int host_dtype);
 int  ink_sync_io(ink_ctx* c);   /* all outstanding copies and the compute stream are done */
 
+/* System::checkNanAndInf (src/systemHelpers.cpp:212-241) as one device reduction: out[0] = grid cells + particles with a NaN / Inf
+ * component (velocity of every cell; position and velocity of every particle), out[1] = cells + particles whose velocity norm
+ * is not < 10000.  Both 0 = the reference's asserts would pass.  8 bytes cross PCIe, not the state.  Multi-GPU: collective. */
+int  ink_check_finite(ink_ctx* c, int64_t out[2]);
+/* Phantom-cell state (out-of-grid particles create map cells that only ever receive dt*g and enter calcTimeStep's
+ * maximum, src/waterSolver.cpp:13-38,158-191): have = any such cell exists, v = their common velocity.  For checkpoints. */
+int  ink_get_phantom(ink_ctx* c, int32_t* have, double v[3]);
+int  ink_set_phantom(ink_ctx* c, int32_t have, const double v[3]);
+/* The ctx's cudaStream_t (as void*): record events on it to time the library, or make it wait on yours.  No reference equivalent. */
+int  ink_get_stream(ink_ctx* c, void** cuda_stream);
 int  ink_get_stats(ink_ctx* c, ink_stats* out);
 /* Device-time of every phase of the last ink_step in ms: dt, advect, forces, viscosity, pressure, vorticity, particles, resort */
 int  ink_get_phase_ms(ink_ctx* c, float out[8]);

@@ -31,6 +31,7 @@ class InkStats(C.Structure):
     _fields_ = [
         ("dt", C.c_double), ("cg_iters", C.c_int32), ("cg_rel_residual", C.c_double), ("advect_skipped", C.c_int32),
         ("steps", C.c_int64), ("resorts", C.c_int64), ("kernel_launches", C.c_int64),
+        ("cg_converged", C.c_int32), ("graph_launches", C.c_int32),
     ]
 
 
@@ -74,6 +75,10 @@ SYMBOLS = {
     "ink_commit_positions": (_I, [_VP, _I]),
     "ink_fetch_positions_async": (_I, [_VP, _I, _VP, _I]),
     "ink_sync_io": (_I, [_VP]),
+    "ink_check_finite": (_I, [_VP, C.POINTER(C.c_int64)]),
+    "ink_get_phantom": (_I, [_VP, C.POINTER(C.c_int32), C.POINTER(C.c_double)]),
+    "ink_set_phantom": (_I, [_VP, C.c_int32, C.POINTER(C.c_double)]),
+    "ink_get_stream": (_I, [_VP, C.POINTER(_VP)]),
     "ink_get_stats": (_I, [_VP, C.POINTER(InkStats)]),
     "ink_get_phase_ms": (_I, [_VP, C.POINTER(C.c_float)]),
 }

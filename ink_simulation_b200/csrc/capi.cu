@@ -77,7 +77,7 @@ struct CtxBase {
     ink_params P;
     std::string err;
     ink_stats stats{};
-    cudaStream_t stream = 0;
+    cudaStream_t stream = nullptr;   // the ctx's own non-blocking stream (created in init; never the legacy NULL stream)
     virtual ~CtxBase() {}
     virtual int init() = 0;
     virtual int set_particles(int drop, const void* pos, const void* vel, int64_t n, int dt) = 0;
@@ -112,6 +112,9 @@ struct CtxBase {
     virtual int fetch_positions_async(int drop, void* pos, int hd) = 0;
     virtual int sync_io() = 0;
     virtual int phase_ms(float out[8]) = 0;
+    virtual int check_finite(int64_t out[2]) = 0;
+    virtual int get_phantom(int32_t* have, double v[3]) = 0;
+    virtual int set_phantom(int32_t have, const double v[3]) = 0;
 };
 
 template <class Real>
@@ -208,6 +211,7 @@ struct Ctx final : CtxBase {
     int in_next = 0, out_next = 0, in_pending = -1, in_pending_drop = -1, in_pending_hd = 32;
 
     ~Ctx() override {
+        if (stream) cudaStreamSynchronize(stream);
         for (int r = 0; r < world && r < kP2pMaxRanks; ++r)
             if (p2p && r != rank && peers.base[r]) cudaIpcCloseMemHandle(peers.base[r]);
         cudaFree(arena);
@@ -236,6 +240,7 @@ struct Ctx final : CtxBase {
         }
         if (s_in) cudaStreamDestroy(s_in);
         if (s_out) cudaStreamDestroy(s_out);
+        if (stream) cudaStreamDestroy(stream);
     }
     void free_particles() {
         for (auto& pp : part) {
@@ -258,6 +263,9 @@ struct Ctx final : CtxBase {
         for (int r = 0; r <= world; ++r) slab_lo[r] = (int)((long long)p.Y * r / world);
         if (world > 1 && p.Y / world < 4) { err = "y-slab decomposition needs at least 4 grid rows per rank"; return 2; }
         CK(cudaSetDevice(p.device));
+        // Own non-blocking stream: the library neither serialises against nor is serialised by the legacy NULL stream (a host
+        // process with a blocking stream of its own would otherwise interleave with every one of the step's launches).
+        CK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
         cudaDeviceProp prop;
         CK(cudaGetDeviceProperties(&prop, p.device));
         if (prop.major < 10) { err = "libinkb200 is built for sm_100a (B200) only"; return 3; }
@@ -293,8 +301,8 @@ struct Ctx final : CtxBase {
         CK(cudaMallocHost(&hS, sizeof(CgScal)));
         CK(cudaMalloc(&seed, g.n)); CK(cudaMemsetAsync(seed, 0, g.n, stream));
         CK(cudaMalloc(&mark, g.n)); CK(cudaMemsetAsync(mark, 0, g.n, stream));
-        CK(cudaMalloc(&d_scal, 4 * sizeof(unsigned int))); CK(cudaMemsetAsync(d_scal, 0, 4 * sizeof(unsigned int), stream));
-        CK(cudaMallocHost(&h_scal, 4 * sizeof(unsigned int)));
+        CK(cudaMalloc(&d_scal, 8 * sizeof(unsigned int))); CK(cudaMemsetAsync(d_scal, 0, 8 * sizeof(unsigned int), stream));   // [4..8): check_finite counters
+        CK(cudaMallocHost(&h_scal, 8 * sizeof(unsigned int)));
         // counting-sort scratch: per-cell counts + scan levels
         if ((long long)kBinsPerCell * g.n >= (1ll << 32)) { err = "grid too large for 32-bit particle bin keys"; return 2; }
         CK(cudaMalloc(&bin_count, (size_t)kBinsPerCell * g.n * sizeof(uint32_t)));
@@ -333,17 +341,19 @@ struct Ctx final : CtxBase {
         off_band[0] = head + 2 * halo; off_band[1] = head + 2 * halo + band;
         const size_t bytes = head + 2 * halo + 2 * band;
         CK(cudaMalloc(&arena, bytes));
-        CK(cudaMemset(arena, 0, bytes));
+        CK(cudaMemsetAsync(arena, 0, bytes, stream));
+        CK(cudaStreamSynchronize(stream));
         cudaIpcMemHandle_t mine;
         CK(cudaIpcGetMemHandle(&mine, arena));
         static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
         unsigned char* hbuf = nullptr;
         CK(cudaMalloc(&hbuf, (size_t)world * 64));
-        CK(cudaMemcpy(hbuf + (size_t)rank * 64, &mine, 64, cudaMemcpyHostToDevice));
+        CK(cudaMemcpyAsync(hbuf + (size_t)rank * 64, &mine, 64, cudaMemcpyHostToDevice, stream));
         NK(nccl().AllGather(hbuf + (size_t)rank * 64, hbuf, 64, ncclUint8, comm, stream));
         CK(cudaStreamSynchronize(stream));
         std::vector<cudaIpcMemHandle_t> all((size_t)world);
-        CK(cudaMemcpy(all.data(), hbuf, (size_t)world * 64, cudaMemcpyDeviceToHost));
+        CK(cudaMemcpyAsync(all.data(), hbuf, (size_t)world * 64, cudaMemcpyDeviceToHost, stream));
+        CK(cudaStreamSynchronize(stream));
         cudaFree(hbuf);
         int ok = 1;
         for (int r = 0; r < world; ++r) {
@@ -355,10 +365,11 @@ struct Ctx final : CtxBase {
         // all ranks must agree (a rank that could not map a peer forces everybody back to NCCL)
         int* dok = nullptr;
         CK(cudaMalloc(&dok, sizeof(int)));
-        CK(cudaMemcpy(dok, &ok, sizeof(int), cudaMemcpyHostToDevice));
+        CK(cudaMemcpyAsync(dok, &ok, sizeof(int), cudaMemcpyHostToDevice, stream));
         NK(nccl().AllReduce(dok, dok, 1, ncclInt32, ncclMin, comm, stream));
         CK(cudaStreamSynchronize(stream));
-        CK(cudaMemcpy(&ok, dok, sizeof(int), cudaMemcpyDeviceToHost));
+        CK(cudaMemcpyAsync(&ok, dok, sizeof(int), cudaMemcpyDeviceToHost, stream));
+        CK(cudaStreamSynchronize(stream));
         cudaFree(dok);
         p2p = ok != 0;
         if (rank == 0 && getenv("INK_VERBOSE")) fprintf(stderr, "[inkb200] world %d: per-iteration exchanges over %s\n", world, p2p ? "peer memory (CUDA IPC + NVLink stores)" : "NCCL");
@@ -483,7 +494,7 @@ struct Ctx final : CtxBase {
         if (int rc = to_device(src, (size_t)g.n * sizeof(T), 0, &d)) return rc;
         LAUNCH((k_xyz_to_internal<T, Real>), nblk(g.n), 256, g, (const T*)d, dst);
         CK(cudaGetLastError());
-        if (d == stage) CK(cudaStreamSynchronize(stream));  // staging is reused by the next call
+        CK(cudaStreamSynchronize(stream));  // staging is reused by the next call; a caller's device buffer is free again on return
         return 0;
     }
     template <class T>
@@ -491,6 +502,7 @@ struct Ctx final : CtxBase {
         if (is_device_ptr(dst)) {
             LAUNCH((k_internal_to_xyz<Real, T>), nblk(g.n), 256, g, src, (T*)dst);
             CK(cudaGetLastError());
+            CK(cudaStreamSynchronize(stream));   // device outputs are complete when the call returns (the ctx stream is private)
             return 0;
         }
         LAUNCH((k_internal_to_xyz<Real, T>), nblk(g.n), 256, g, src, (T*)stage);
@@ -981,7 +993,8 @@ struct Ctx final : CtxBase {
                 sw[j] = (Real)std::sqrt(w);
             }
             CK(cudaMalloc(&d_sw, (size_t)g.Y * sizeof(Real)));
-            CK(cudaMemcpy(d_sw, sw.data(), (size_t)g.Y * sizeof(Real), cudaMemcpyHostToDevice));
+            CK(cudaMemcpyAsync(d_sw, sw.data(), (size_t)g.Y * sizeof(Real), cudaMemcpyHostToDevice, stream));
+            CK(cudaStreamSynchronize(stream));   // sw is a local
             const size_t band = (size_t)2 * ovl * g.sy * sizeof(Real);
             for (int b = 0; b < 2; ++b) { CK(cudaMalloc(&band_save[b], band)); CK(cudaMalloc(&band_recv[b], band)); }
         }
@@ -1240,7 +1253,7 @@ struct Ctx final : CtxBase {
         const bool blind = use_mg && !dist && prev_iters > 1;
         auto zero_rhs = [&]() -> int {   // f == 0: the solution is exactly 0
             CK(cudaMemsetAsync(x, 0, (size_t)g.n * sizeof(Real), stream));
-            stats.cg_iters = 0; stats.cg_rel_residual = 0;
+            stats.cg_iters = 0; stats.cg_rel_residual = 0; stats.cg_converged = 1;
             return 0;
         };
         if (blind) hS->done = 0;   // the mirror still holds the previous solve's head; refreshed at the first poll
@@ -1306,11 +1319,20 @@ struct Ctx final : CtxBase {
                         std::chrono::duration<double, std::micro>(t_enq - t_batch).count(), std::chrono::duration<double, std::micro>(t_done - t_enq).count());
             }
             if (hS->bb == 0.0) { tr_dump(); return zero_rhs(); }   // only reachable on the blind path (checked up front otherwise)
+            // a NaN / Inf residual never satisfies rr <= tol^2 bb: stop here instead of running cg_max_iters garbage iterations
+            // (the reference asserts in checkNanAndInf, src/systemHelpers.cpp:212-241)
+            if (!std::isfinite(hS->rr) || !std::isfinite(hS->bb) || !std::isfinite(hS->rz)) {
+                tr_dump();
+                stats.cg_iters = hS->iters; stats.cg_converged = 0; stats.cg_rel_residual = NAN;
+                err = "pressure solve: non-finite residual (NaN/Inf in the velocity field or right-hand side)";
+                return 5;
+            }
         }
         tr_dump();
         prev_iters = hS->iters;
         stats.cg_iters = hS->iters;
         stats.cg_rel_residual = std::sqrt(hS->rr / hS->bb);
+        stats.cg_converged = hS->done ? 1 : 0;   // 0: stopped at cg_max_iters (callers that fix the iteration count expect that)
         return 0;
     }
 
@@ -1437,6 +1459,37 @@ struct Ctx final : CtxBase {
         if (dt_out) *dt_out = dt_;
         return 0;
     }
+    // System::checkNanAndInf (src/systemHelpers.cpp:212-241) on the device: out[0] = grid cells / particles with a NaN or Inf
+    // component, out[1] = those whose velocity norm is not < 10000.  Multi-GPU: own rows and own particles, summed over ranks.
+    int check_finite(int64_t out[2]) override {
+        unsigned long long* d_chk = reinterpret_cast<unsigned long long*>(d_scal + 4);
+        unsigned long long* h_chk = reinterpret_cast<unsigned long long*>(h_scal + 4);
+        CK(cudaMemsetAsync(d_chk, 0, 2 * sizeof(unsigned long long), stream));
+        const long long cells = (long long)(g.j1 - g.j0) * g.sy, base = (long long)g.j0 * g.sy;
+        auto blocks = [](long long n) { return (unsigned int)std::min<long long>(kSMs * 8, std::max<long long>(1, (n + 255) / 256)); };
+        LAUNCH((k_check_finite<Real>), blocks(cells), 256, cells, U(0) + base, U(1) + base, U(2) + base, 1, d_chk);   // old == curr between steps
+        if (np > 0) {
+            LAUNCH((k_check_finite<Real>), blocks(np), 256, np, part[pcur].p[0], part[pcur].p[1], part[pcur].p[2], 0, d_chk);
+            LAUNCH((k_check_finite<Real>), blocks(np), 256, np, part[pcur].v[0], part[pcur].v[1], part[pcur].v[2], 1, d_chk);
+        }
+        CK(cudaGetLastError());
+        if (int rc = allreduce(d_chk, 2, ncclUint64, ncclSum)) return rc;
+        read_small(h_chk, d_chk, 2 * sizeof(unsigned long long));
+        CK(cudaStreamSynchronize(stream));
+        out[0] = (int64_t)h_chk[0]; out[1] = (int64_t)h_chk[1];
+        return 0;
+    }
+    // phantom-cell state (Q8): part of what a checkpoint must carry for calcTimeStep to resume bit for bit
+    int get_phantom(int32_t* have, double v[3]) override {
+        *have = have_phantom ? 1 : 0;
+        for (int a = 0; a < 3; ++a) v[a] = (double)phantom_v[a];
+        return 0;
+    }
+    int set_phantom(int32_t have, const double v[3]) override {
+        have_phantom = have != 0;
+        for (int a = 0; a < 3; ++a) phantom_v[a] = (Real)v[a];
+        return 0;
+    }
     int phase_ms(float out[8]) override {
         if (!ev_valid) { err = "no ink_step yet"; return 2; }
         CK(cudaEventSynchronize(ev[8]));
@@ -1536,6 +1589,10 @@ int ink_commit_positions(ink_ctx* c, int drop) { return c->impl->commit_position
 int ink_fetch_positions_async(ink_ctx* c, int drop, void* pos, int hd) { return c->impl->fetch_positions_async(drop, pos, hd); }
 int ink_sync_io(ink_ctx* c) { return c->impl->sync_io(); }
 
+int ink_check_finite(ink_ctx* c, int64_t out[2]) { return c->impl->check_finite(out); }
+int ink_get_phantom(ink_ctx* c, int32_t* have, double v[3]) { return c->impl->get_phantom(have, v); }
+int ink_set_phantom(ink_ctx* c, int32_t have, const double v[3]) { return c->impl->set_phantom(have, v); }
+int ink_get_stream(ink_ctx* c, void** cuda_stream) { *cuda_stream = (void*)c->impl->stream; return 0; }
 int ink_get_stats(ink_ctx* c, ink_stats* out) { *out = c->impl->stats; return 0; }
 int ink_get_phase_ms(ink_ctx* c, float out[8]) { return c->impl->phase_ms(out); }
 

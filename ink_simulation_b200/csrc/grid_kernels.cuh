@@ -158,6 +158,28 @@ __global__ void __launch_bounds__(256) k_max_speed(Grid g, const Real* __restric
     block_max_to_global(m, out);
 }
 
+// System::checkNanAndInf (src/systemHelpers.cpp:212-241) as ONE device reduction over n (x, y, z) triples: the reference
+// asserts, per grid cell and per particle, no NaN / Inf component and norm() < 10000.  counts[0] += triples with a
+// non-finite component, counts[1] += triples whose norm is not < 10000 (a NaN norm fails that test, as in the reference).
+// check_norm = 0: positions (the reference only tests them for NaN / Inf).  8 bytes come back instead of the whole state.
+template <class Real>
+__global__ void __launch_bounds__(256) k_check_finite(long long n, const Real* __restrict__ x, const Real* __restrict__ y, const Real* __restrict__ z,
+                                                      int check_norm, unsigned long long* __restrict__ counts) {
+    INK_PDL();
+    unsigned int bad = 0, big = 0;
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) {
+        const Real a = x[t], b = y[t], c = z[t];
+        if (!(isfinite(a) && isfinite(b) && isfinite(c))) ++bad;
+        if (check_norm && !(norm3(a, b, c) < Real(10000))) ++big;
+    }
+    bad = __reduce_add_sync(0xffffffffu, bad);
+    big = __reduce_add_sync(0xffffffffu, big);
+    if ((threadIdx.x & 31) == 0) {
+        if (bad) atomicAdd(counts, (unsigned long long)bad);
+        if (big) atomicAdd(counts + 1, (unsigned long long)big);
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // K1  nearest-cell semi-Lagrangian convection — System::applyConvection + traceParticle
 // (src/waterSolver.cpp:98-128; Q6, Q7).  old (u,v,w) -> curr (nu,nv,nw).

@@ -227,7 +227,8 @@ void InkSim::writeWaterGridVelocities() {
 
 // ---- checkpoint / resume ------------------------------------------------------------------------------------------------
 // State of a run between two steps = currVelocity (old == curr there, src/waterSolver.cpp:92-95), the particles, and — ours
-// only — the start vector of the next pressure solve.  Everything else the library keeps (force-mask seeds, max speed,
+// only — the start vector of the next pressure solve and the phantom-cell velocity (Q8; meta.txt, as double bits).
+// Payloads are the reference's fp32 .ply: a precision = 64 context resumes to fp32 rounding, not bit for bit.  Everything else the library keeps (force-mask seeds, max speed,
 // particle bins, curl) is recomputed from these, and none of it depends on the particle order in memory.
 void InkSim::writeCheckpoint() {
     drain();
@@ -255,6 +256,12 @@ void InkSim::writeCheckpoint() {
     if (!f) throw std::runtime_error("cannot write " + dir + "/meta.txt");
     std::fprintf(f, "grid %d %d %d\ndrops %d\nnext_frame %d\ntime_since_last_render_bits 0x%08x\n", WATERGRID_X, WATERGRID_Y, WATERGRID_Z, drops,
                  m_nextFrame, bits);
+    // phantom cells of out-of-grid particles: their accumulated velocity enters calcTimeStep's maximum
+    double pv[3] = {0, 0, 0};
+    const int have = ink_system.getPhantom(pv) ? 1 : 0;
+    unsigned long long pb[3];
+    std::memcpy(pb, pv, sizeof pb);
+    std::fprintf(f, "phantom %d 0x%016llx 0x%016llx 0x%016llx\n", (int)have, pb[0], pb[1], pb[2]);
     std::fclose(f);
 }
 
@@ -265,6 +272,9 @@ bool InkSim::resume() {
     int X = 0, Y = 0, Z = 0, drops = 0, frame = 1;
     unsigned int bits = 0;
     const int got = std::fscanf(f, "grid %d %d %d drops %d next_frame %d time_since_last_render_bits 0x%x", &X, &Y, &Z, &drops, &frame, &bits);
+    int have = 0;
+    unsigned long long pb[3] = {0, 0, 0};
+    const bool got_phantom = (got == 6) && std::fscanf(f, " phantom %d 0x%llx 0x%llx 0x%llx", &have, &pb[0], &pb[1], &pb[2]) == 4;   // absent in older checkpoints
     std::fclose(f);
     if (got != 6) throw std::runtime_error("malformed " + dir + "/meta.txt");
     if (X != WATERGRID_X || Y != WATERGRID_Y || Z != WATERGRID_Z) throw std::runtime_error("checkpoint is for another grid size");
@@ -288,6 +298,11 @@ bool InkSim::resume() {
     ink_system.setVelocityField(u.data(), v.data(), w.data());
     ink_system.setWarmStart(q.data());
     for (int d = 0; d < drops; d++) ink_system.setInk(d, pos[d].data(), vel[d].data(), (long long)(pos[d].size() / 3));
+    if (got_phantom) {   // after setInk: seeding the force mask from the restored particles must not redefine it
+        double pv[3];
+        std::memcpy(pv, pb, sizeof pv);
+        ink_system.setPhantom(have != 0, pv);
+    }
     float since;
     std::memcpy(&since, &bits, sizeof since);
     m_nextFrame = frame;

@@ -107,6 +107,14 @@ void System::setVelocityField(const float* u, const float* v, const float* w) {
 void System::setWarmStart(const float* q) {
     if (ink_set_warm_start(m_ctx, q, 32) != 0) fail("ink_set_warm_start");
 }
+bool System::getPhantom(double v[3]) {
+    int32_t have = 0;
+    if (ink_get_phantom(m_ctx, &have, v) != 0) fail("ink_get_phantom");
+    return have != 0;
+}
+void System::setPhantom(bool have, const double v[3]) {
+    if (ink_set_phantom(m_ctx, have ? 1 : 0, v) != 0) fail("ink_set_phantom");
+}
 void System::setInk(int drop, const float* xyz, const float* vel, long long n) {
     if (drop < 0 || drop > (int)m_ink.size()) throw std::runtime_error("setInk: drop index out of range");
     if (drop == (int)m_ink.size()) m_ink.emplace_back();
@@ -162,18 +170,14 @@ const std::unordered_map<Vector3i, Cell, hash_func> System::getWaterGrid() {
     return m_waterGrid;
 }
 
-// checkNanAndInf (src/systemHelpers.cpp:212-241): assert-only in the reference; here it throws.
+// checkNanAndInf (src/systemHelpers.cpp:212-241): assert-only in the reference; here it throws.  The tests themselves (no NaN / Inf
+// component, norm() < 10000 on every cell velocity and particle velocity) run on the device as one reduction
+// (ink_check_finite): two counters come back, not the grid and every Particle.
 void System::checkNanAndInf() {
-    const size_t n = (size_t)WATERGRID_X * WATERGRID_Y * WATERGRID_Z;
-    std::vector<float> f[3] = {std::vector<float>(n), std::vector<float>(n), std::vector<float>(n)};
-    copyVelocityField(f[0].data(), f[1].data(), f[2].data());
-    for (const auto& a : f)
-        for (float x : a)
-            if (!std::isfinite(x)) throw std::runtime_error("checkNanAndInf: non-finite grid velocity");
-    for (const auto& ink : getInkParticles())
-        for (const Particle& p : ink)
-            for (int a = 0; a < 3; ++a)
-                if (!std::isfinite(p.position[a]) || !std::isfinite(p.velocity[a])) throw std::runtime_error("checkNanAndInf: non-finite particle");
+    int64_t bad[2] = {0, 0};
+    if (ink_check_finite(m_ctx, bad) != 0) fail("ink_check_finite");
+    if (bad[0] != 0) throw std::runtime_error("checkNanAndInf: " + std::to_string(bad[0]) + " grid cells / particles hold a NaN or Inf");
+    if (bad[1] != 0) throw std::runtime_error("checkNanAndInf: " + std::to_string(bad[1]) + " velocities with norm() >= 10000");
 }
 
 std::ostream& operator<<(std::ostream& strm, const Cell& obj) {

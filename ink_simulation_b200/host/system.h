@@ -129,6 +129,8 @@ public:
     void setVelocityField(const float* u, const float* v, const float* w);
     void setWarmStart(const float* q);
     void setInk(int drop, const float* xyz, const float* vel, long long n);   // replace (or append) one drop
+    bool getPhantom(double v[3]);                                // phantom-cell state for checkpoints
+    void setPhantom(bool have, const double v[3]);
 
 private:
     ink_ctx* m_ctx = nullptr;

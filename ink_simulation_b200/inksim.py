@@ -10,7 +10,7 @@ the reference's non-standard format token included — src/inkSim.cpp:62-68, :10
     <dir>/checkpoint/velocityField.ply x y z u v w           same format, state between two steps
     <dir>/checkpoint/warmstart.ply     x y z q               start vector of the next pressure solve (ink_get_warm_start)
     <dir>/checkpoint/drop<i>.ply       x y z vx vy vz        particles of drop i
-    <dir>/checkpoint/meta.txt          grid, drops, next frame number, time since the last frame (float bits)
+    <dir>/checkpoint/meta.txt          grid, drops, next frame number, time since the last frame (float bits), phantom-cell velocity (Q8, double bits)
 """
 import os
 import struct
@@ -122,6 +122,8 @@ class InkSim:
         with open(os.path.join(ck, "meta.txt"), "w") as f:
             f.write("grid %d %d %d\ndrops %d\nnext_frame %d\ntime_since_last_render_bits 0x%08x\n"
                     % (*S.dims, S.num_drops(), self._next_frame, bits))
+            have, pv = S.get_phantom()   # phantom cells of out-of-grid particles (Q8) enter calcTimeStep's maximum
+            f.write("phantom %d %s\n" % (int(have), " ".join("0x%016x" % struct.unpack("<Q", struct.pack("<d", x))[0] for x in pv)))
 
     def resume(self):
         S = self.ink_system
@@ -147,6 +149,8 @@ class InkSim:
         S.set_warm_start(q[:, 3].reshape(S.dims))
         for d, rec in enumerate(parts):
             S.set_particles(rec[:, :3], rec[:, 3:], drop=d)
+        if "phantom" in kv:   # absent in checkpoints written before the phantom state was saved
+            S.set_phantom(int(kv["phantom"][0]), [struct.unpack("<d", struct.pack("<Q", int(x, 16)))[0] for x in kv["phantom"][1:4]])
         self._next_frame = int(kv["next_frame"][0])
         self._since = np.float32(struct.unpack("<f", struct.pack("<I", int(kv["time_since_last_render_bits"][0], 16)))[0])
         self._resumed = True

@@ -41,6 +41,10 @@ def _ptr(a):
     if isinstance(a, np.ndarray):
         return a.ctypes.data_as(C.c_void_p)
     if hasattr(a, "data_ptr"):  # torch tensor (host pinned or device) — plumbing only
+        if getattr(a, "is_cuda", False):   # the ctx runs on its own non-blocking stream: device inputs must be complete (ink_capi.h)
+            import torch
+
+            torch.cuda.current_stream(a.device).synchronize()
         return C.c_void_p(a.data_ptr())
     return C.c_void_p(int(a))
 
@@ -204,12 +208,31 @@ class System:
         """currVelocity of every cell as three dense (X,Y,Z) arrays."""
         return self.get_field("curr")
 
+    def check_finite(self):
+        """(non-finite count, norm >= 10000 count) over grid velocities and particles: the tests of System::checkNanAndInf
+        (src/systemHelpers.cpp:212-241) as one device reduction (ink_check_finite)."""
+        out = (C.c_int64 * 2)()
+        self._ck(self.L.ink_check_finite(self.h, out))
+        return int(out[0]), int(out[1])
+
     def checkNanAndInf(self):
-        u, v, w = self.get_field("curr")
-        for a in (u, v, w):
-            assert np.isfinite(a).all()
-        for pos, vel in self.getInkParticles():
-            assert np.isfinite(pos).all() and np.isfinite(vel).all()
+        bad, big = self.check_finite()
+        if bad or big:
+            raise InkError(f"checkNanAndInf: {bad} grid cells / particles hold a NaN or Inf, {big} velocities with norm() >= 10000")
+
+    def get_phantom(self):
+        have, v = C.c_int32(), (C.c_double * 3)()
+        self._ck(self.L.ink_get_phantom(self.h, C.byref(have), v))
+        return bool(have.value), tuple(v)
+
+    def set_phantom(self, have, v):
+        self._ck(self.L.ink_set_phantom(self.h, int(bool(have)), (C.c_double * 3)(*[float(x) for x in v])))
+
+    def cuda_stream(self):
+        """the ctx's own non-blocking cudaStream_t as an int (ink_get_stream); wrap it with torch.cuda.ExternalStream to record events"""
+        s = C.c_void_p()
+        self._ck(self.L.ink_get_stream(self.h, C.byref(s)))
+        return s.value or 0
 
     # ---- state
     def set_particles(self, pos, vel=None, drop=0):

@@ -132,6 +132,45 @@ def test_gpu_python_checkpoint_resume_is_bit_exact(tmp_path):
 
 
 @pytest.mark.gpu
+def test_gpu_checkpoint_carries_the_phantom_cell_state(tmp_path):
+    """out-of-grid particles create phantom cells whose accumulated dt*g enters calcTimeStep's maximum (Q8).  With
+    every particle above the grid at step 0 the grid itself is still at rest after that step, so the phantom term IS the
+    maximum: a resume that dropped it would take dt_min instead.  The checkpoint carries it (meta.txt, double bits):
+    resumed run == uninterrupted run, bit for bit, dt included."""
+    from ink_simulation_b200 import System
+
+    def make():
+        S = System(*C1, arith="strict")
+        pos = seeding.box_scene(C1, 2000)
+        pos[:, 1] = C1[1] + 0.75                   # above the grid: phantom cells at step 0, clamped inside by the particle update
+        S.set_particles(pos)
+        return S
+
+    render, n1, n2 = 0.05, 1, 12
+    straight = inksim.InkSim(tmp_path / "a", make())
+    straight.simulate(render, n1)
+    have, pv = straight.ink_system.get_phantom()
+    assert have and pv[1] < 0                      # the phantom cells received dt*g at step 0
+    straight.writeCheckpoint()
+    assert "phantom 1 " in open(tmp_path / "a" / "checkpoint" / "meta.txt").read()
+    shutil.copytree(tmp_path / "a", tmp_path / "b")
+    again = inksim.InkSim(tmp_path / "b", make())
+    assert again.resume()
+    assert again.ink_system.get_phantom() == (have, pv)
+    want = straight.ink_system.calc_dt(0.045)
+    assert again.ink_system.calc_dt(0.045) == want
+    again.ink_system.set_phantom(False, (0, 0, 0))  # the term matters here: without it the resumed run would take another step
+    assert again.ink_system.calc_dt(0.045) != want
+    again.ink_system.set_phantom(have, pv)
+    straight._resumed = True
+    straight.simulate(render, n2)
+    again.simulate(render, n2)
+    assert straight.ink_system.stats().dt == again.ink_system.stats().dt
+    for x, y in zip(state(straight.ink_system), state(again.ink_system)):
+        assert np.array_equal(x, y)
+
+
+@pytest.mark.gpu
 def test_gpu_cpp_binary_checkpoint_resume_and_cross_host(tmp_path):
     exe = os.path.join(HOST, "inksim_b200_c1")
     assert os.path.exists(exe), "build with __graft_entry__.build()"
@@ -188,6 +227,8 @@ class FakeSystem:
     def get_particles(self, d=0): return self.pos.copy(), self.vel.copy()
     def get_velocity(self): return [a.copy() for a in self.u]
     def get_warm_start(self): return self.q.copy()
+    def get_phantom(self): return getattr(self, "phantom", (False, (0.0, 0.0, 0.0)))
+    def set_phantom(self, have, v): self.phantom = (bool(have), tuple(float(x) for x in v))
     def set_velocity(self, u, v, w): self.u = [np.array(a, np.float32) for a in (u, v, w)]
     def set_warm_start(self, q): self.q = np.array(q, np.float32)
     def set_particles(self, pos, vel=None, drop=0): self.pos, self.vel = np.array(pos, np.float32), np.array(vel, np.float32)

@@ -307,3 +307,85 @@ def test_gpu_zero_rhs_after_a_developed_solve():
         T.pressure(0.17)
     assert util.rel_inf(np.stack(A.get_velocity()), np.stack(B.get_velocity())) < 1e-5
     A.close(); B.close()
+
+
+def test_gpu_check_finite_is_the_reference_checkNanAndInf(oracle_mod):
+    """System::checkNanAndInf (src/systemHelpers.cpp:212-241): no NaN / Inf component, norm() < 10000 — as one device
+    reduction returning two counters.  Clean state passes; every kind of violation is counted where the reference asserts."""
+    from ink_simulation_b200 import InkError
+
+    dims = util.C1
+    S = gpu(dims)
+    u, v, w = util.rand_field(dims, 41, scale=0.5)
+    S.set_velocity(u, v, w)
+    S.set_particles(util.box_particles(dims, 5000, 42))
+    S.solve(0.35)
+    assert S.check_finite() == (0, 0)
+    S.checkNanAndInf()
+    bad_u = u.copy(); bad_u[1, 2, 3] = np.nan; bad_u[2, 2, 2] = np.inf
+    big_v = v.copy(); big_v[3, 3, 3] = 2e4                      # finite, but norm() >= 10000
+    S.set_velocity(bad_u, big_v, w)
+    assert S.check_finite() == (2, 3)                           # NaN and Inf norms also fail `< 10000`, as in the reference
+    with pytest.raises(InkError, match="checkNanAndInf"):
+        S.checkNanAndInf()
+    S.set_velocity(u, v, w)
+    pos = util.box_particles(dims, 100, 43)
+    vel = np.zeros_like(pos)
+    pos[7, 1] = np.nan                                          # position: NaN / Inf only
+    vel[9, 0] = 10000.0                                         # exactly 10000 is not < 10000
+    vel[11, 2] = -np.inf
+    S.set_particles(pos, vel)
+    assert S.check_finite() == (2, 2)
+    S.close()
+
+
+def test_gpu_solver_stops_on_non_finite_residual():
+    """A NaN in the field makes rr NaN, which never satisfies rr <= tol^2 bb: ink_step must fail at the first poll instead of
+    running cg_max_iters garbage iterations and returning 0 (the reference aborts in checkNanAndInf)."""
+    import time
+
+    from ink_simulation_b200 import InkError
+
+    dims = util.C2
+    S = gpu(dims)
+    u, v, w = util.rand_field(dims, 44, scale=0.5)
+    u[3, 4, 5] = np.nan
+    S.set_velocity(u, v, w)
+    t0 = time.perf_counter()
+    with pytest.raises(InkError, match="non-finite"):
+        S.pressure(0.17)
+    assert time.perf_counter() - t0 < 2.0
+    assert S.stats().cg_converged == 0 and S.stats().cg_iters < 100
+    S.close()
+
+
+def test_gpu_library_runs_on_its_own_non_blocking_stream():
+    """the ctx owns a cudaStreamNonBlocking stream (never the NULL stream); device-pointer inputs produced on torch's
+    stream are picked up correctly through the Python host, device outputs are complete on return."""
+    import torch
+
+    dims = util.C1
+    S = gpu(dims)
+    assert S.cuda_stream() != 0
+    ext = torch.cuda.ExternalStream(S.cuda_stream())
+    u, v, w = util.rand_field(dims, 45, scale=0.5)
+    host = gpu(dims)
+    host.set_velocity(u, v, w)
+    # produce the inputs on torch's stream with a long-running chain in front of them
+    big = torch.randn(4096, 4096, device="cuda")
+    for _ in range(10):
+        big = big @ big * 1e-3
+    tu, tv, tw = (torch.from_numpy(a).cuda() + 0 * big[0, 0] for a in (u, v, w))
+    S.set_velocity(tu.contiguous(), tv.contiguous(), tw.contiguous())
+    for a, b in zip(S.get_velocity(), host.get_velocity()):
+        np.testing.assert_array_equal(a, b)
+    # events recorded on the ctx stream see the library's work
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    S.set_particles(util.box_particles(dims, 10000, 46))
+    e0.record(ext)
+    for _ in range(5):
+        S.solve(0.35)
+    e1.record(ext)
+    e1.synchronize()
+    assert e0.elapsed_time(e1) > 0.05
+    S.close(); host.close()
