@@ -48,6 +48,14 @@ def build(force: bool = False) -> None:
     subprocess.check_call([os.path.join(_HERE, "build_ref.sh")], stdout=subprocess.DEVNULL)
 
 
+def set_threads(n=None) -> int:
+    """OpenMP threads of the oracle port: n, or every CPU this process may run on (sched_getaffinity) — NOT what
+    OMP_NUM_THREADS says (torchrun exports 1).  Returns the team size omp_get_max_threads() then reports."""
+    L = _load_oracle()
+    L.orc_set_threads(C.c_int(int(n) if n else len(os.sched_getaffinity(0))))
+    return int(L.orc_max_threads())
+
+
 def have_ref() -> bool:
     return os.path.exists(REF_SO)
 

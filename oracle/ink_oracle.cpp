@@ -21,6 +21,7 @@
 #include <array>
 #include <type_traits>
 #include <chrono>
+#include <omp.h>
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
@@ -631,6 +632,10 @@ double orc_solve_timed(void* h, double ttnr, double* t) {
     });
     return dt;
 }
+// OpenMP team size of this library: torchrun exports OMP_NUM_THREADS=1 to every rank, so bench.py sets the count explicitly
+// (and reports what omp_get_max_threads() then says, not os.cpu_count()).
+void orc_set_threads(int n) { if (n > 0) omp_set_num_threads(n); }
+int orc_max_threads() { return omp_get_max_threads(); }
 int orc_num_phantom(void* h) { int r = 0; DISPATCH(h, { r = (int)o.phantom.size(); }); return r; }
 
 }  // extern "C"

@@ -74,3 +74,4 @@ if __name__ == "__main__":
     make(util.C1, 11, 2000)
     make(util.ODD, 23, 500)
     make((14, 30, 14), 37, 1500)
+    make(util.C2, 53, 100000)   # BASELINE config 2 (20x45x20, 100 k particles): the largest scene the reference itself runs (17 s LU set-up)

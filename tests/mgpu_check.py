@@ -6,7 +6,8 @@ Every rank builds (a) the y-slab / particle-shard DISTRIBUTED System over NCCL a
 whole problem on its own device, steps both from the same seeded state and compares:
   * phases without a solve (forces, viscosity, vorticity, particles): bit-exact (same kernels, redundant-row scheme),
   * pressure / full steps: within the north_star tolerances (the slab-local preconditioner changes the CG iterates,
-    not the solution): projected velocity 1e-5 field-relative, particle positions 1e-6 relative per step.
+    not the solution): projected velocity 1e-5 field-relative PER PHASE inside whole steps, particle positions 1e-6
+    relative per step.
 Exit code 0 = all ranks agree.  Used by tests/test_multi_gpu.py (-m gpu, skipped with < 2 GPUs)."""
 import os
 import sys
@@ -35,7 +36,9 @@ def main():
         if not ok:
             failures.append(f"rank {rank}: {name} {info}")
 
-    cases = (((16, 5 * world, 12), 5000), ((16, 40, 12), 20000), ((32, 64, 32), 200000))
+    # the last case has >= 32 rows per rank (>= 2 * ovl = 16) and Z % 4 == 0: the vectorised band kernels, the fused peer-store
+    # pushes and interior ranks with TWO neighbours are what runs there
+    cases = (((16, 5 * world, 12), 5000), ((16, 40, 12), 20000), ((32, 64, 32), 200000), ((64, 32 * world, 64), 2000000))
     if os.environ.get("MGPU_CASES"):   # e.g. MGPU_CASES=0,2: run a subset (debugging at large world sizes)
         cases = tuple(cases[int(i)] for i in os.environ["MGPU_CASES"].split(","))
     for dims, npart in cases:
@@ -69,16 +72,35 @@ def main():
             check(f"{dims} pressure[{precond}]", ev < 1e-5 and ep < 2e-5, f"vel {ev:.2e} p {ep:.2e} iters {D.stats().cg_iters}/{S.stats().cg_iters}")
             check(f"{dims} divergence[{precond}]", np.abs(D.divergence()).max() <= np.abs(S.divergence()).max() * 1.01 + 1e-5)
             D.close(); S.close()
-        # --- whole steps, re-synchronised after each (parity is judged per step from identical input)
+        # --- whole steps, PHASE BY PHASE from identical input (as tests/test_gpu_parity.py::test_gpu_step_phase_by_phase does
+        # against the oracle): stencil phases bit-exact, projected velocity 1e-5 of the field scale, then — from the single-GPU
+        # projected field — vorticity and particles bit-exact
         D, S = pair()
         for step in range(4):
-            dtd, dts = D.solve(0.35), S.solve(0.35)
-            check(f"{dims} step {step} dt", dtd == dts, f"{dtd} {dts}")
+            dt = S.calc_dt(0.35)
+            check(f"{dims} step {step} dt", D.calc_dt(0.35) == dt)
+            for ph in ("advect", "forces", "viscosity"):
+                getattr(D, ph)(dt); getattr(S, ph)(dt)
+                check(f"{dims} step {step} {ph}", np.array_equal(np.stack(D.get_velocity()), np.stack(S.get_velocity())))
+            D.pressure(dt); S.pressure(dt)
             vd, vs = np.stack(D.get_velocity()), np.stack(S.get_velocity())
-            check(f"{dims} step {step} velocity", util.rel_inf(vd, vs) < 5e-4, f"{util.rel_inf(vd, vs):.2e}")
+            check(f"{dims} step {step} projected velocity", util.rel_inf(vd, vs) < 1e-5, f"{util.rel_inf(vd, vs):.2e} iters {D.stats().cg_iters}/{S.stats().cg_iters}")
+            check(f"{dims} step {step} divergence", np.abs(D.divergence()).max() <= np.abs(S.divergence()).max() * 1.01 + 1e-5 * np.abs(vs).max())
+            D.set_velocity(*S.get_velocity())
+            D.vorticity(dt); S.vorticity(dt)
+            check(f"{dims} step {step} vorticity", np.array_equal(np.stack(D.get_velocity()), np.stack(S.get_velocity())))
+            D.particles(dt); S.particles(dt)
+            pd, vd = D.get_particles(); ps, vs = S.get_particles()
+            check(f"{dims} step {step} particles", np.array_equal(pd, ps[lo:hi]) and np.array_equal(vd, vs[lo:hi]))
+        # --- and undivided System::solve calls, re-synchronised after each: dt equal, particle positions 1e-6 relative per step
+        for step in range(3):
+            dtd, dts = D.solve(0.35), S.solve(0.35)
+            check(f"{dims} solve {step} dt", dtd == dts, f"{dtd} {dts}")
             pd = D.get_particles()[0]; ps = S.get_particles()[0]
             rel = np.max(np.abs(pd - ps[lo:hi]) / np.maximum(np.abs(ps[lo:hi]), 1.0)) if hi > lo else 0.0
-            check(f"{dims} step {step} particles", rel < 1e-6, f"{rel:.2e}")
+            check(f"{dims} solve {step} particles", rel < 1e-6, f"{rel:.2e}")
+            bad, big = D.check_finite()
+            check(f"{dims} solve {step} check_finite", bad == 0 and big == 0, f"{bad} {big}")
             D.set_velocity(*S.get_velocity())
             D.set_particles(ps, S.get_particles()[1])
         if rank == 0:
