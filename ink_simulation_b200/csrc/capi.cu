@@ -65,6 +65,19 @@ static inline void launch_k(void (*kern)(KArgs...), unsigned int grid, unsigned 
     cfg.attrs = at; cfg.numAttrs = g_use_pdl ? 1 : 0;
     cudaLaunchKernelEx(&cfg, kern, KArgs(std::forward<Args>(args))...);
 }
+// one thread-block cluster of `ctas` CTAs (grid == cluster), with the same programmatic-serialization attribute
+template <class... KArgs, class... Args>
+static inline void launch_cluster(void (*kern)(KArgs...), unsigned int ctas, unsigned int block, size_t smem, cudaStream_t st, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(ctas); cfg.blockDim = dim3(block); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[2];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = ctas; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = g_use_pdl ? 2 : 1;
+    cudaLaunchKernelEx(&cfg, kern, KArgs(std::forward<Args>(args))...);
+}
 #define LAUNCH(kern, grid, block, ...)                                   \
     do {                                                                 \
         launch_k(kern, (grid), (block), 0, stream, __VA_ARGS__);         \
@@ -144,6 +157,7 @@ struct Ctx final : CtxBase {
     size_t mg_tail_cap = 200 * 1024;   // INK_MG_TAIL_KB: shared-memory budget of the single-block tail (experiments)
     int mg_lc = -1;           // >= 1: levels [mg_lc, mg_lt] run in ONE persistent launch (k_mg3_coarse); -1: per-level kernels
     unsigned int* mg_bar = nullptr;
+    int mg_cluster = 0;       // > 0: the coarse levels run as one thread-block cluster of this many CTAs (k_mg3_coarse<Real, true>)
     bool mg_tri = false;   // trilinear V(1,1) (mg_tri.cuh) instead of piecewise-constant V(2,2) (mg.cuh)
     int prev_iters = 0;
     // multi-GPU: overlapping-Schwarz extension of the slab the V-cycle runs on (mg_vec.cuh)
@@ -154,6 +168,13 @@ struct Ctx final : CtxBase {
     Real* band_recv[2] = {nullptr, nullptr};
     CgScal* S = nullptr;
     CgScal* hS = nullptr;  // pinned mirror of the scalar head
+    // One PCG iteration (CG pair + V-cycle, ~13-20 kernel nodes with their programmatic-dependency edges) captured once as a
+    // CUDA graph per direction-buffer parity and replayed: one host call per iteration instead of one per kernel.  Kernels
+    // launched after convergence exit on S->done, so replaying a fixed body is legal.  INK_NO_GRAPH=1 = direct launches.
+    cudaGraphExec_t it_graph[2] = {nullptr, nullptr};
+    const void* it_graph_x = nullptr;     // the solution vector the cached graphs were captured for
+    long long it_graph_nodes = 0;
+    bool use_graph = true;
     // multi-GPU: per-iteration exchanges by peer stores over NVLink (p2p.cuh) instead of NCCL calls
     bool p2p = false;
     // INK_TRACE_ITER=k: CUDA-event timeline of CG iteration k of every solve, printed by rank 0 (diagnostic)
@@ -195,6 +216,12 @@ struct Ctx final : CtxBase {
     std::vector<uint32_t*> scan_lvl;  // tile sums per level
     std::vector<long long> scan_n;
     long long since_sort = 0;
+    // K8 tile path (particle_kernels.cuh: TMA-staged shared-memory tiles): work list of slot chunks, rebuilt at every re-binning
+    uint2* tile_work = nullptr;
+    unsigned int* tile_nwork = nullptr;
+    long long tile_work_cap = 0;
+    int tile_chunk = 0;        // > 0: the tile kernel runs with chunks of at most this many slots
+    int tile_mode = 1;         // INK_K8_TILE: 0 off, 1 automatic (dense clouds, 16-byte rows), 2 forced wherever it is legal
     // staging for host <-> device conversion
     void* stage = nullptr;
     size_t stage_bytes = 0;
@@ -212,6 +239,7 @@ struct Ctx final : CtxBase {
 
     ~Ctx() override {
         if (stream) cudaStreamSynchronize(stream);
+        for (auto& ge : it_graph) if (ge) cudaGraphExecDestroy(ge);
         for (int r = 0; r < world && r < kP2pMaxRanks; ++r)
             if (p2p && r != rank && peers.base[r]) cudaIpcCloseMemHandle(peers.base[r]);
         cudaFree(arena);
@@ -226,6 +254,7 @@ struct Ctx final : CtxBase {
         cudaFree(d_sw);
         for (auto p : band_save) cudaFree(p);
         for (auto p : band_recv) cudaFree(p);
+        cudaFree(tile_nwork);
         cudaFree(S); cudaFreeHost(hS); cudaFree(seed); cudaFree(mark); cudaFree(d_scal); cudaFreeHost(h_scal);
         free_particles();
         cudaFree(bin_count);
@@ -250,6 +279,7 @@ struct Ctx final : CtxBase {
         }
         cudaFree(bin_key); cudaFree(bin_rank);
         bin_key = bin_rank = nullptr;
+        cudaFree(tile_work); tile_work = nullptr; tile_work_cap = 0;
         pcap = 0;
     }
 
@@ -315,6 +345,10 @@ struct Ctx final : CtxBase {
             scan_n.push_back(m);
         }
         for (auto& e : ev) CK(cudaEventCreate(&e));
+        if (const char* e = getenv("INK_K8_TILE")) tile_mode = atoi(e);
+        CK(cudaMalloc(&tile_nwork, sizeof(unsigned int)));
+        CK(cudaFuncSetAttribute((k_particles_rk2_tile<Real, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, kTileSmemBytes));
+        CK(cudaFuncSetAttribute((k_particles_rk2_tile<Real, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, kTileSmemBytes));
         if (P.cg_precond == INK_PCG_MG || P.cg_precond == INK_PCG_MG_TRI) {
             mg_tri = (P.cg_precond == INK_PCG_MG_TRI);
             if (int rc = mg_setup()) return rc;
@@ -746,6 +780,35 @@ struct Ctx final : CtxBase {
         CK(cudaGetLastError());
         pcur ^= 1;
         ++stats.resorts;
+        return tile_plan();
+    }
+    // Decide whether K8 runs in its tile form for the current cloud and, if so, cut every half-row's slot range into chunks.
+    // Chunk size: the largest multiple of 256 slots (<= 1024) whose expected tile — a chunk of a uniform cloud spans
+    // w = chunk / (particles per half cell column) cells in x: 9 w + 21 z-rows — stays under 40 KB (the kernel has 56 KB).
+    int tile_plan() {
+        tile_chunk = 0;
+        if (tile_mode == 0 || np == 0 || !C.unit_h || g.n >= (1ll << 31) || ((size_t)g.Z * sizeof(Real)) % 16 != 0) return 0;
+        const double per_half_col = (double)np / (2.0 * g.X * g.Y);
+        int chunk = 0;
+        for (int ch = 256 * kTileKP; ch >= 256; ch -= 256) {
+            const double w = ch / std::max(per_half_col, 1e-9);
+            if ((9.0 * w + 21.0) * g.Z * sizeof(Real) <= 40.0 * 1024) { chunk = ch; break; }
+        }
+        const long long max_work = (np + 255) / 256 + 2ll * g.Y + 1;
+        if (tile_mode == 1) {
+            if (chunk == 0) return 0;                                         // sparse cloud or very long rows: tiles would not fit
+            if ((double)np / ((double)np / chunk + 2.0 * g.Y) < 128.0) return 0;   // too few particles per staged tile to pay for it
+        } else if (chunk == 0) chunk = 256;
+        if (max_work > tile_work_cap) {
+            if (tile_work) CK(cudaFree(tile_work));
+            tile_work = nullptr; tile_work_cap = 0;
+            CK(cudaMalloc(&tile_work, (size_t)max_work * sizeof(uint2)));
+            tile_work_cap = max_work;
+        }
+        CK(cudaMemsetAsync(tile_nwork, 0, sizeof(unsigned int), stream));
+        LAUNCH(k_tile_worklist, (unsigned int)(2 * g.Y), 128, g.X, g.Y, g.Z, np, (const uint32_t*)bin_count, chunk, tile_work, tile_nwork);
+        CK(cudaGetLastError());
+        tile_chunk = chunk;
         return 0;
     }
     int ensure_seed() {
@@ -970,6 +1033,7 @@ struct Ctx final : CtxBase {
     int mg_setup() {
         if (const char* e = getenv("INK_TRACE_ITER")) trace_iter = atoi(e);
         if (const char* e = getenv("INK_HOSTTIME")) host_timing = atoi(e) != 0;
+        if (const char* e = getenv("INK_NO_GRAPH")) use_graph = (atoi(e) == 0);
         if (const char* e = getenv("INK_MG3_UNFUSED")) mg_fuse = (atoi(e) == 0);
         if (const char* e = getenv("INK_MG_TAIL_KB")) mg_tail_cap = (size_t)std::max(1, atoi(e)) * 1024;
         // measured (B200, 128x256x128): a tail holding only the coarsest (<= 1024-cell) level beats a deeper single-block tail
@@ -1049,20 +1113,50 @@ struct Ctx final : CtxBase {
         want = std::max(want, mg_tail_smem);
         CK(cudaFuncSetAttribute(k_mg_tail<Real>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)want));
         CK(cudaFuncSetAttribute(k_mg3_tail<Real>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)want));
-        // Persistent coarse-level kernel: OFF by default.  Measured on B200 (128x256x128): 63 us for levels 2..4 in one launch
-        // (7 device-side grid barriers, 32 blocks) against ~40 us for the same levels as 10 PDL-chained launches that use the
-        // whole GPU; step 2.35 vs 1.97 ms.  Kept opt-in (INK_MG_COARSE=1) as the starting point for a cluster/DSMEM version.
-        if (mg_tri && getenv("INK_MG_COARSE") && atoi(getenv("INK_MG_COARSE")) != 0) {
+        // Coarse levels (<= kMg3CoarseCells cells: launch-latency bound, ~4.5 us per kernel for < 1 us of work) in ONE launch.
+        // INK_MG_COARSE=2: one thread-block cluster of 16 CTAs with the hardware cluster barrier between passes (falls back to 8
+        // CTAs, then to per-level kernels, if the device refuses the cluster).  INK_MG_COARSE=1: the round-1 variant, a 32-block
+        // co-resident grid with a global-memory barrier.  Default 0: per-level kernels.  Measured on B200 at 128x256x128 (round 2,
+        // profiles/r2_c_*): the PDL-chained launch train that uses all 148 SMs (pressure phase 0.97 ms) beats both single-launch
+        // variants (cluster of 16: 1.29 ms, of 8: 1.36 ms; grid barrier: slower still) — on 16 SMs the passes themselves are
+        // latency-bound (a few warps per scheduler walking L2-latency load chains), which costs more than the launches save.
+        int coarse_mode = 0;
+        if (const char* e = getenv("INK_MG_COARSE")) coarse_mode = mg_tri ? atoi(e) : 0;
+        int coarse_cells = kMg3CoarseCells;
+        if (const char* e = getenv("INK_MG_COARSE_CELLS")) coarse_cells = std::max(1, atoi(e));
+        if (coarse_mode != 0) {
             for (int l = 1; l < mg_lt; ++l) {
                 const MgDims& d = lv[l].d;
-                if ((long long)d.X * (d.j1 - d.j0) * d.Z <= kMg3CoarseCells) { mg_lc = l; break; }
+                if ((long long)d.X * (d.j1 - d.j0) * d.Z <= coarse_cells) { mg_lc = l; break; }
             }
             if (mg_lc >= 1 && mg_lt - mg_lc + 1 > kMg3CoarseMaxLevels) mg_lc = -1;
-            if (mg_lc >= 1) {
-                CK(cudaMalloc(&mg_bar, 2 * sizeof(unsigned int)));
-                CK(cudaMemsetAsync(mg_bar, 0, 2 * sizeof(unsigned int), stream));
-                CK(cudaFuncSetAttribute(k_mg3_coarse<Real>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)want));
+        }
+        if (mg_lc >= 1 && coarse_mode == 1) {
+            CK(cudaMalloc(&mg_bar, 2 * sizeof(unsigned int)));
+            CK(cudaMemsetAsync(mg_bar, 0, 2 * sizeof(unsigned int), stream));
+            CK(cudaFuncSetAttribute((k_mg3_coarse<Real, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)want));
+        } else if (mg_lc >= 1) {
+            CK(cudaFuncSetAttribute((k_mg3_coarse<Real, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)want));
+            mg_cluster = kMg3ClusterCtas;
+            if (const char* e = getenv("INK_MG_CLUSTER_CTAS")) mg_cluster = std::max(1, std::min(16, atoi(e)));
+            if (mg_cluster > 8 && cudaFuncSetAttribute((k_mg3_coarse<Real, true>), cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
+                cudaGetLastError();
+                mg_cluster = 8;
             }
+            // can the device co-schedule such a cluster at all?
+            while (mg_cluster >= 2) {
+                cudaLaunchConfig_t cfg = {};
+                cfg.gridDim = dim3(mg_cluster); cfg.blockDim = dim3(kMg3CoarseThreads); cfg.dynamicSmemBytes = mg_tail_smem;
+                cudaLaunchAttribute at[1];
+                at[0].id = cudaLaunchAttributeClusterDimension;
+                at[0].val.clusterDim.x = mg_cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+                cfg.attrs = at; cfg.numAttrs = 1;
+                int ncl = 0;
+                if (cudaOccupancyMaxActiveClusters(&ncl, (k_mg3_coarse<Real, true>), &cfg) == cudaSuccess && ncl >= 1) break;
+                cudaGetLastError();
+                mg_cluster /= 2;
+            }
+            if (mg_cluster < 2) { mg_cluster = 0; mg_lc = -1; }
         }
         use_mg = true;
         return 0;
@@ -1102,7 +1196,8 @@ struct Ctx final : CtxBase {
                 A.tail = mg_tail;
                 A.tail_off = (long long)lv[mg_lt].d.j0 * lv[mg_lt].d.X * lv[mg_lt].d.Z;
                 A.bar = mg_bar;
-                launch_k(k_mg3_coarse<Real>, kMg3CoarseBlocks, kMg3CoarseThreads, mg_tail_smem, stream, S, A);
+                if (mg_cluster > 0) launch_cluster(k_mg3_coarse<Real, true>, mg_cluster, kMg3CoarseThreads, mg_tail_smem, stream, S, A);
+                else launch_k(k_mg3_coarse<Real, false>, kMg3CoarseBlocks, kMg3CoarseThreads, mg_tail_smem, stream, S, A);
                 ++stats.kernel_launches;
                 TR("coarse levels");
             } else {
@@ -1232,6 +1327,33 @@ struct Ctx final : CtxBase {
         ++stats.kernel_launches;
         return 0;
     }
+    // capture `body(dc)` once per parity into a graph (thread-local capture mode: other host threads of the process are not
+    // affected), then replay it.  The cached pair belongs to one solution vector x; another x recaptures.
+    template <class Body>
+    int replay_iteration(int dc, const void* x, Body& body) {
+        if (it_graph_x != x) {
+            for (auto& ge : it_graph) if (ge) { cudaGraphExecDestroy(ge); ge = nullptr; }
+            it_graph_x = x;
+        }
+        if (!it_graph[dc]) {
+            const long long before = stats.kernel_launches;
+            cudaGraph_t gr = nullptr;
+            CK(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
+            const int rc = body(dc);
+            const cudaError_t ce = cudaStreamEndCapture(stream, &gr);
+            if (rc) { if (gr) cudaGraphDestroy(gr); return rc; }
+            if (ce != cudaSuccess) { err = std::string("graph capture of the PCG iteration failed: ") + cudaGetErrorString(ce); return 1; }
+            it_graph_nodes = stats.kernel_launches - before;
+            stats.kernel_launches = before;   // capturing launched nothing
+            const cudaError_t ie = cudaGraphInstantiate(&it_graph[dc], gr, 0);
+            cudaGraphDestroy(gr);
+            if (ie != cudaSuccess) { it_graph[dc] = nullptr; err = std::string("cudaGraphInstantiate failed: ") + cudaGetErrorString(ie); return 1; }
+        }
+        CK(cudaGraphLaunch(it_graph[dc], stream));
+        stats.kernel_launches += it_graph_nodes;
+        ++stats.graph_launches;
+        return 0;
+    }
     int cg_solve(const Real* f, Real* x) {
         const unsigned int nb = cg_blocks();
         const bool dist = world > 1;
@@ -1274,37 +1396,46 @@ struct Ctx final : CtxBase {
         // host polls convergence every `every` iterations; kernels launched after convergence are no-ops (S->done).
         // With the preconditioner the count is small and steady from step to step: launch last solve's count first.
         const int every = use_mg ? 2 : std::max(1, P.cg_check_every);
+        // one PCG iteration: direction + matvec, update, preconditioner (+ the distributed reductions / exchanges)
+        auto iteration_body = [&](int dc) -> int {
+            TR("start");
+            if (vec4()) LAUNCH((k_cg_dir_matvec<Real, 4>), nb, 256, g, S, zsrc, cg_d[dc], cg_d[dc ^ 1], cg_w, hlo, hhi);
+            else LAUNCH((k_cg_dir_matvec<Real, 1>), nb, 256, g, S, zsrc, cg_d[dc], cg_d[dc ^ 1], cg_w, hlo, hhi);
+            TR("matvec");
+            if (dist) {
+                if (int rc = ar_post(0, 1, 1)) return rc;
+            }
+            TR("allreduce dw");
+            const P2pPush push = make_push();
+            if (vec4()) {
+                if (use_mg) LAUNCH((k_cg_update<Real, 4, true>), nb, 256, g, S, x, cg_r, cg_d[dc ^ 1], cg_w, push);
+                else LAUNCH((k_cg_update<Real, 4, false>), nb, 256, g, S, x, cg_r, cg_d[dc ^ 1], cg_w, push);
+            } else {
+                if (use_mg) LAUNCH((k_cg_update<Real, 1, true>), nb, 256, g, S, x, cg_r, cg_d[dc ^ 1], cg_w, push);
+                else LAUNCH((k_cg_update<Real, 1, false>), nb, 256, g, S, x, cg_r, cg_d[dc ^ 1], cg_w, push);
+            }
+            TR("update");
+            if (use_mg)
+                if (int rc = precondition(cg_r)) return rc;
+            if (dist) {
+                if (int rc = ar_post(1, 2, 2)) return rc;
+                TR("allreduce rr,rz");
+                if (!use_mg)
+                    if (int rc = halo_exchange(zsrc, 1, 1)) return rc;
+            }
+            return 0;
+        };
+        // graph replay: single GPU (the distributed body carries host-side sequence numbers in its kernel arguments), not while tracing
+        const bool graph_ok = use_graph && !dist && trace_iter < 0;
         while (!hS->done && launched < P.cg_max_iters) {
             int batch = std::min(every, P.cg_max_iters - launched);
             const auto t_batch = std::chrono::steady_clock::now();
             if (use_mg && launched == 0 && prev_iters > 1) batch = std::min(prev_iters, P.cg_max_iters);
             for (int it = 0; it < batch; ++it) {
                 tracing = (trace_iter >= 0 && launched + it == trace_iter);
-                TR("start");
-                if (vec4()) LAUNCH((k_cg_dir_matvec<Real, 4>), nb, 256, g, S, zsrc, cg_d[dcur], cg_d[dcur ^ 1], cg_w, hlo, hhi);
-                else LAUNCH((k_cg_dir_matvec<Real, 1>), nb, 256, g, S, zsrc, cg_d[dcur], cg_d[dcur ^ 1], cg_w, hlo, hhi);
-                TR("matvec");
-                if (dist) {
-                    if (int rc = ar_post(0, 1, 1)) return rc;
-                }
-                TR("allreduce dw");
-                const P2pPush push = make_push();
-                if (vec4()) {
-                    if (use_mg) LAUNCH((k_cg_update<Real, 4, true>), nb, 256, g, S, x, cg_r, cg_d[dcur ^ 1], cg_w, push);
-                    else LAUNCH((k_cg_update<Real, 4, false>), nb, 256, g, S, x, cg_r, cg_d[dcur ^ 1], cg_w, push);
-                } else {
-                    if (use_mg) LAUNCH((k_cg_update<Real, 1, true>), nb, 256, g, S, x, cg_r, cg_d[dcur ^ 1], cg_w, push);
-                    else LAUNCH((k_cg_update<Real, 1, false>), nb, 256, g, S, x, cg_r, cg_d[dcur ^ 1], cg_w, push);
-                }
-                TR("update");
-                if (use_mg)
-                    if (int rc = precondition(cg_r)) return rc;
-                if (dist) {
-                    if (int rc = ar_post(1, 2, 2)) return rc;
-                    TR("allreduce rr,rz");
-                    if (!use_mg)
-                        if (int rc = halo_exchange(zsrc, 1, 1)) return rc;
-                }
+                if (graph_ok) {
+                    if (int rc = replay_iteration(dcur, x, iteration_body)) return rc;
+                } else if (int rc = iteration_body(dcur)) return rc;
                 dcur ^= 1;
                 tracing = false;
             }
@@ -1422,7 +1553,12 @@ struct Ctx final : CtxBase {
         CK(cudaMemsetAsync(seed, 0, g.n, stream));
         const bool fast = P.arith == INK_ARITH_FAST, uh = C.unit_h && g.n < (1ll << 31);
 #define INK_K8(F, H) LAUNCH((k_particles_rk2<Real, F, H>), nblk(np), 256, g, C, dt, np, part[pcur], U(0), U(1), U(2), seed)
-        if (fast) { if (uh) INK_K8(true, true); else INK_K8(true, false); }
+        if (tile_chunk > 0 && uh) {   // TMA-staged shared-memory tiles; upper bound on the work items, surplus blocks exit at once
+            const unsigned int nb = (unsigned int)((np + tile_chunk - 1) / tile_chunk + 2ll * g.Y);
+            if (fast) launch_k((k_particles_rk2_tile<Real, true>), nb, kTileThreads, (size_t)kTileSmemBytes, stream, g, C, dt, part[pcur], U(0), U(1), U(2), seed, tile_work, tile_nwork);
+            else launch_k((k_particles_rk2_tile<Real, false>), nb, kTileThreads, (size_t)kTileSmemBytes, stream, g, C, dt, part[pcur], U(0), U(1), U(2), seed, tile_work, tile_nwork);
+            ++stats.kernel_launches;
+        } else if (fast) { if (uh) INK_K8(true, true); else INK_K8(true, false); }
         else { if (uh) INK_K8(false, true); else INK_K8(false, false); }
 #undef INK_K8
         CK(cudaGetLastError());

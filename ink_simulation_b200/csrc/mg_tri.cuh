@@ -520,6 +520,7 @@ __global__ void __launch_bounds__(kMgTailThreads) k_mg3_tail(CgScal* S, MgTailAr
 // written in exactly one pass and only read in later passes, so no SM can hold a stale L1 line for it.
 constexpr int kMg3CoarseCells = 131072;
 constexpr int kMg3CoarseBlocks = 32;
+constexpr int kMg3ClusterCtas = 16;     // non-portable cluster size (opt-in attribute); 8 is the portable maximum
 constexpr int kMg3CoarseThreads = 512;
 constexpr int kMg3CoarseMaxLevels = 6;
 
@@ -550,16 +551,29 @@ struct Mg3CoarseArgs {
     unsigned int* bar;
 };
 
-template <class Real>
+// hardware barrier across the CTAs of a thread-block cluster (sm_90+): release on arrive, acquire on wait, cluster scope —
+// global-memory writes of every CTA before the barrier are visible to every CTA after it
+__device__ __forceinline__ void mg_cluster_barrier() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+// CLUSTER = false: a co-resident grid of kMg3CoarseBlocks blocks with a global-memory barrier (round 1: 63 us for levels 2-4 at
+// 128x256x128, slower than the launch train — each barrier is an atomic + a spin through L2).
+// CLUSTER = true : ONE thread-block cluster (kMg3ClusterCtas CTAs, launched with cudaLaunchAttributeClusterDimension); the
+// barrier between passes is the hardware cluster barrier (sub-microsecond).  Level arrays stay in global memory = L2 (written
+// in exactly one pass, read only in later passes, so no SM can hold a stale L1 line); CTA 0 runs the shared-memory tail.
+template <class Real, bool CLUSTER>
 __global__ void __launch_bounds__(kMg3CoarseThreads) k_mg3_coarse(CgScal* S, Mg3CoarseArgs<Real> A) {
     asm volatile("griddepcontrol.wait;" ::: "memory");
     if (S->done) return;                       // uniform: nobody writes `done` during this launch
     const unsigned int gtid = blockIdx.x * blockDim.x + threadIdx.x, gnth = gridDim.x * blockDim.x;
+    auto barrier = [&]() { if (CLUSTER) mg_cluster_barrier(); else mg_grid_barrier(A.bar); };
     for (int q = 0; q + 1 < A.nlev; ++q) {     // down
         const MgDims &df = A.lv[q].d, &dc = A.lv[q + 1].d;
         if (df.Z % 4 == 0) mg3_residual_rz_v4_dev<Real>(df, A.lv[q].r, A.lv[q].xb, gtid, gnth);
         else mg3_residual<Real>(df, A.lv[q].r, A.lv[q].xb, gtid, gnth);
-        mg_grid_barrier(A.bar);
+        barrier();
         if (df.Z % 4 == 0 && dc.Z % 4 == 0) mg3_restrict_xy_v4_dev<Real>(df, dc, A.lv[q].xb, A.lv[q + 1].r, gtid, gnth);
         else if (df.Z % 4 == 0) {              // z-restricted residual, scalar x-y gather
             INK_MG_CELL_LOOP(dc, gtid, gnth) {
@@ -578,13 +592,13 @@ __global__ void __launch_bounds__(kMg3CoarseThreads) k_mg3_coarse(CgScal* S, Mg3
                 A.lv[q + 1].r[c] = acc;
             }
         } else mg3_restrict<Real>(df, dc, A.lv[q].xb, A.lv[q + 1].r, gtid, gnth);
-        mg_grid_barrier(A.bar);
+        barrier();
     }
     if (blockIdx.x == 0) mg3_tail_dev<Real>(S, A.tail, A.lv[A.nlev - 1].r + A.tail_off, A.lv[A.nlev - 1].xa + A.tail_off);
-    mg_grid_barrier(A.bar);
+    barrier();
     for (int q = A.nlev - 2; q >= 0; --q) {    // up
         mg3_up<Real>(A.lv[q].d, A.lv[q + 1].d, A.lv[q].s, A.lv[q].r, A.lv[q + 1].xa, A.lv[q].xa, gtid, gnth);
-        if (q > 0) mg_grid_barrier(A.bar);
+        if (q > 0) barrier();
     }
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 }

@@ -10,6 +10,7 @@
 #include "common.cuh"
 #include "grid_kernels.cuh"
 #include "sample3.cuh"
+#include "tma.cuh"
 
 namespace ink {
 
@@ -67,6 +68,172 @@ __global__ void __launch_bounds__(256) k_particles_rk2(Grid g, Consts<Real> C, R
     } else {
         long long c;
         if (cell_of_point(g, x, y, z, c)) seed[c] = 1;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K8, tile version: the velocity rows a chunk of binned particles can touch are staged in SHARED MEMORY by the TMA unit
+// (cp.async.bulk + mbarrier, tma.cuh) and the 48 corner gathers per particle read shared memory instead of L1/L2.
+//
+// Why: ncu r1_e — the global-gather kernel moves 7.2 sectors per request through L1 (a warp's 32 lanes hit 2.6 distinct
+// 128-byte lines per gather, 48 gathers per particle) and is L1-wavefront bound at 0.27 of the HBM roofline while DRAM idles.
+// Particles are binned by quarter column (bin_key): one HALF-ROW (j, hy) of the grid is a contiguous slot range ordered by x
+// then z.  A block takes a chunk of <= 256 * kTileKP consecutive slots of one half-row (k_tile_worklist), finds the half-cell
+// bounding box of its particles (so drift since the last re-binning only widens the tile), and stages
+//     u rows  x in [ux0, ux1], y in [uy0, uy1]     v rows  x in [vx0, vx1], y in [vy0, vy1]     w rows  x as v, y as u
+// — each (component, y) an x-run of whole z-rows, i.e. ONE contiguous bulk copy — with one half-cell of margin for the RK2
+// midpoint (CFL: it moves < 0.1 cell).  A sample whose 24 corners are not all inside the tile (wild dt, walls: the tile is
+// clipped to the grid, so "inside the tile" implies "inside the grid") takes the global-memory sampler: results never depend
+// on the tile.  Arithmetic per sample is the same eval_strict / eval_fast on the same eight values: strict stays bit-exact.
+// ------------------------------------------------------------------------------------------------
+constexpr int kTileThreads = 256;
+constexpr int kTileKP = 4;                       // particles per thread at most (chunk <= 1024 slots)
+constexpr int kTileSmemBytes = 56 * 1024;        // 4 blocks per SM
+
+// one block per half-row r = 2j + hy: split its slot range into equal chunks of at most `chunk` slots
+__global__ void __launch_bounds__(128) k_tile_worklist(int X, int Y, int Z, long long np, const uint32_t* __restrict__ bin_off, int chunk,
+                                                       uint2* __restrict__ work, unsigned int* __restrict__ nwork) {
+    INK_PDL();
+    __shared__ unsigned int base;
+    const int r = blockIdx.x;
+    const long long row_keys = 2ll * X * Z;
+    const long long begin = bin_off[(long long)r * row_keys];
+    const long long end = (r + 1 == 2 * Y) ? np : (long long)bin_off[(long long)(r + 1) * row_keys];
+    const long long cnt = end - begin;
+    if (cnt <= 0) return;
+    const long long nch = (cnt + chunk - 1) / chunk, per = (cnt + nch - 1) / nch;
+    if (threadIdx.x == 0) base = atomicAdd(nwork, (unsigned int)nch);
+    __syncthreads();
+    for (long long c = threadIdx.x; c < nch; c += blockDim.x) {
+        const long long b0 = begin + c * per, b1 = (b0 + per < end) ? b0 + per : end;
+        work[base + c] = (b0 < b1) ? make_uint2((uint32_t)b0, (uint32_t)b1) : make_uint2(0u, 0u);
+    }
+}
+
+template <class Real>
+struct TileGeom {
+    int ux0, uy0, vx0, vy0;          // first staged row of the u / v tiles (w: x as v, y as u)
+    unsigned int unx1, uny1, vnx1, vny1;   // extents minus one: (unsigned)(ix - ux0) < unx1  <=>  ix and ix + 1 are staged
+    int Z, usy, vsy;                 // row stride (elements) and y strides of the u and v / w tiles
+    int bv, bw;                      // element offsets of the v and w tiles
+};
+
+template <class Real>
+__device__ __forceinline__ void load8s(const Real* p, int sx, int sy, Real (&f)[8]) {   // shared-memory corners, order of load8
+    f[0] = p[0];       f[4] = p[1];
+    f[1] = p[sx];      f[5] = p[sx + 1];
+    f[2] = p[sy];      f[6] = p[sy + 1];
+    f[3] = p[sy + sx]; f[7] = p[sy + sx + 1];
+}
+
+// get_velocity3's interior path on the staged tile; false = not all corners staged (caller takes the global sampler)
+template <class Real, bool FAST>
+__device__ __forceinline__ bool get_velocity3_tile(const Real* tile, const TileGeom<Real>& T, Real px, Real py, Real pz, Real& ox, Real& oy, Real& oz) {
+    const Real xh = px - Real(0.5f), yh = py - Real(0.5f), zh = pz - Real(0.5f);
+    const Real fx = rfloor(px), fy = rfloor(py), fz = rfloor(pz);
+    const Real fxh = rfloor(xh), fyh = rfloor(yh), fzh = rfloor(zh);
+    // NaN / huge coordinates: the float -> int conversion saturates (cvt.rzi), the range tests below then fail
+    const int ix = (int)fx, jy = (int)fy, kz = (int)fz, ixh = (int)fxh, jyh = (int)fyh, kzh = (int)fzh;
+    const unsigned int ax = (unsigned int)(ix - T.ux0), ay = (unsigned int)(jyh - T.uy0), bx = (unsigned int)(ixh - T.vx0), by = (unsigned int)(jy - T.vy0);
+    if (!(ax < T.unx1 && ay < T.uny1 && bx < T.vnx1 && by < T.vny1 && kzh >= 0 && kz <= T.Z - 2)) return false;
+    const int Z = T.Z;
+    const Real* pu = tile + ((int)ay * (int)(T.unx1 + 1) + (int)ax) * Z + kzh;
+    const Real* pv = tile + T.bv + ((int)by * (int)(T.vnx1 + 1) + (int)bx) * Z + kzh;
+    const Real* pw = tile + T.bw + ((int)ay * (int)(T.vnx1 + 1) + (int)bx) * Z + kz;
+    Real f[8];
+    if (FAST) {
+        const Real tx = px - fx, ty = py - fy, tz = pz - fz, txh = xh - fxh, tyh = yh - fyh, tzh = zh - fzh;
+        load8s(pu, Z, T.usy, f);  ox = eval_fast(f, tx, tyh, tzh);
+        load8s(pv, Z, T.vsy, f);  oy = eval_fast(f, txh, ty, tzh);
+        load8s(pw, Z, T.vsy, f);  oz = eval_fast(f, txh, tyh, tz);
+    } else {
+        load8s(pu, Z, T.usy, f);  ox = eval_strict(f, px, fx, yh, fyh, zh, fzh);
+        load8s(pv, Z, T.vsy, f);  oy = eval_strict(f, xh, fxh, py, fy, zh, fzh);
+        load8s(pw, Z, T.vsy, f);  oz = eval_strict(f, xh, fxh, yh, fyh, pz, fz);
+    }
+    return true;
+}
+
+template <class Real, bool FAST>
+__global__ void __launch_bounds__(kTileThreads, 4) k_particles_rk2_tile(Grid g, Consts<Real> C, Real dt, Particles<Real> P,
+                                                                         const Real* __restrict__ u, const Real* __restrict__ v, const Real* __restrict__ w,
+                                                                         uint8_t* __restrict__ seed, const uint2* __restrict__ work,
+                                                                         const unsigned int* __restrict__ nwork) {
+    INK_PDL();
+    if (blockIdx.x >= *nwork) return;
+    const uint2 wk = work[blockIdx.x];
+    if (wk.x >= wk.y) return;
+    extern __shared__ __align__(16) unsigned char tile_raw[];
+    Real* tile = reinterpret_cast<Real*>(tile_raw);
+    __shared__ uint64_t bar;
+    __shared__ int red[4][kTileThreads / 32];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    if (tid == 0) mbar_init(&bar, 1);
+    // this thread's particles + the half-cell bounding box of the block's particles
+    Real x[kTileKP], y[kTileKP], z[kTileKP];
+    int gx0 = 0x7fffffff, gx1 = -1, hy0 = 0x7fffffff, hy1 = -1;
+    const Real gxm = Real(2 * g.X - 1), hym = Real(2 * g.Y - 1);
+#pragma unroll
+    for (int q = 0; q < kTileKP; ++q) {
+        const unsigned int s = wk.x + tid + q * kTileThreads;
+        if (s < wk.y) {
+            x[q] = ld_stream(P.p[0] + s); y[q] = ld_stream(P.p[1] + s); z[q] = ld_stream(P.p[2] + s);
+            const int gx = (int)fmin(fmax(rfloor(x[q] + x[q]), Real(0)), gxm), hy = (int)fmin(fmax(rfloor(y[q] + y[q]), Real(0)), hym);
+            gx0 = min(gx0, gx); gx1 = max(gx1, gx); hy0 = min(hy0, hy); hy1 = max(hy1, hy);
+        }
+    }
+    gx0 = __reduce_min_sync(0xffffffffu, gx0); gx1 = __reduce_max_sync(0xffffffffu, gx1);
+    hy0 = __reduce_min_sync(0xffffffffu, hy0); hy1 = __reduce_max_sync(0xffffffffu, hy1);
+    if (lane == 0) { red[0][wid] = gx0; red[1][wid] = gx1; red[2][wid] = hy0; red[3][wid] = hy1; }
+    __syncthreads();   // also: the initialised mbarrier is visible to every thread
+#pragma unroll
+    for (int q = 0; q < kTileThreads / 32; ++q) { gx0 = min(gx0, red[0][q]); gx1 = max(gx1, red[1][q]); hy0 = min(hy0, red[2][q]); hy1 = max(hy1, red[3][q]); }
+    // tile geometry: one half-cell of margin each way for the midpoint, clipped to the grid
+    TileGeom<Real> T;
+    const int ux1 = min(((gx1 + 1) >> 1) + 1, g.X - 1), vx1 = min((gx1 >> 1) + 1, g.X - 1);
+    const int uy1 = min((hy1 >> 1) + 1, g.Y - 1), vy1 = min(((hy1 + 1) >> 1) + 1, g.Y - 1);
+    T.ux0 = max((gx0 - 1) >> 1, 0); T.vx0 = max((gx0 - 2) >> 1, 0);
+    T.uy0 = max((hy0 - 2) >> 1, 0); T.vy0 = max((hy0 - 1) >> 1, 0);
+    const int unx = ux1 - T.ux0 + 1, vnx = vx1 - T.vx0 + 1, uny = uy1 - T.uy0 + 1, vny = vy1 - T.vy0 + 1;
+    T.Z = g.Z; T.usy = unx * g.Z; T.vsy = vnx * g.Z;
+    T.bv = unx * uny * g.Z; T.bw = T.bv + vnx * vny * g.Z;
+    const long long elems = (long long)T.bw + (long long)vnx * uny * g.Z;
+    const bool tile_ok = unx >= 2 && vnx >= 2 && uny >= 2 && vny >= 2 && elems * (long long)sizeof(Real) <= (long long)kTileSmemBytes;
+    T.unx1 = tile_ok ? (unsigned int)(unx - 1) : 0u; T.uny1 = (unsigned int)(uny - 1); T.vnx1 = (unsigned int)(vnx - 1); T.vny1 = (unsigned int)(vny - 1);
+    if (tile_ok) {
+        if (wid == 0) {
+            if (lane == 0) mbar_arrive_expect_tx(&bar, (unsigned int)(elems * sizeof(Real)));
+            __syncwarp();
+            // one bulk copy per (component, y): an x-run of whole z-rows is contiguous in memory
+            for (int c = lane; c < uny + vny + uny; c += 32) {
+                const Real* src; Real* dst; int n;
+                if (c < uny) { src = u + ((long long)(T.uy0 + c) * g.X + T.ux0) * g.Z; dst = tile + c * T.usy; n = T.usy; }
+                else if (c < uny + vny) { const int a = c - uny; src = v + ((long long)(T.vy0 + a) * g.X + T.vx0) * g.Z; dst = tile + T.bv + a * T.vsy; n = T.vsy; }
+                else { const int a = c - uny - vny; src = w + ((long long)(T.uy0 + a) * g.X + T.vx0) * g.Z; dst = tile + T.bw + a * T.vsy; n = T.vsy; }
+                tma_load_1d(dst, src, (unsigned int)(n * sizeof(Real)), &bar);
+            }
+        }
+        mbar_wait(&bar, 0);
+    }
+#pragma unroll
+    for (int q = 0; q < kTileKP; ++q) {
+        const unsigned int s = wk.x + tid + q * kTileThreads;
+        if (s >= wk.y) continue;
+        Real px = x[q], py = y[q], pz = z[q];
+        Real sx, sy, sz;
+        if (!get_velocity3_tile<Real, FAST>(tile, T, px, py, pz, sx, sy, sz)) get_velocity3<Real, FAST, true>(u, v, w, g, C, px, py, pz, sx, sy, sz);
+        Real vx = C.rho * sx, vy = C.rho * sy, vz = C.rho * sz;                       // equation 9
+        const Real mx = px + (vx * dt * Real(.5)), my = py + (vy * dt * Real(.5)), mz = pz + (vz * dt * Real(.5));  // equation 7
+        if (!get_velocity3_tile<Real, FAST>(tile, T, mx, my, mz, sx, sy, sz)) get_velocity3<Real, FAST, true>(u, v, w, g, C, mx, my, mz, sx, sy, sz);
+        const Real wx = C.rho * sx, wy = C.rho * sy, wz = C.rho * sz;
+        px = mx + (dt * wx); py = my + (dt * wy); pz = mz + (dt * wz);              // equation 8 (from the MIDPOINT, Q3)
+        if (px < Real(0) || px > C.bx) { vx *= Real(-1.f); px = rmin(rmax(px, C.lo), C.cx); }
+        if (py < Real(0) || py > C.by) { vy *= Real(-1.f); py = rmin(rmax(py, C.lo), C.cy); }
+        if (pz < Real(0) || pz > C.bz) { vz *= Real(-1.f); pz = rmin(rmax(pz, C.lo), C.cz); }
+        st_stream(P.p[0] + s, px); st_stream(P.p[1] + s, py); st_stream(P.p[2] + s, pz);
+        st_stream(P.v[0] + s, vx); st_stream(P.v[1] + s, vy); st_stream(P.v[2] + s, vz);
+        const int ci = (int)rfloor(px), cj = (int)rfloor(py), ck = (int)rfloor(pz);   // launcher guarantees X*Y*Z < 2^31
+        if ((unsigned)ci < (unsigned)g.X && (unsigned)cj < (unsigned)g.Y && (unsigned)ck < (unsigned)g.Z) seed[(cj * g.X + ci) * g.Z + ck] = 1;
     }
 }
 

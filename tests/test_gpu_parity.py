@@ -389,3 +389,76 @@ def test_gpu_library_runs_on_its_own_non_blocking_stream():
     e1.synchronize()
     assert e0.elapsed_time(e1) > 0.05
     S.close(); host.close()
+
+
+@pytest.fixture
+def k8_tile_env(monkeypatch):
+    """INK_K8_TILE is read when a System is created: 2 = the TMA-staged shared-memory tile kernel wherever it is legal
+    (also for clouds the heuristic would leave to the global-gather kernel), 0 = never."""
+    def make(mode, dims, dtype=np.float32, **kw):
+        monkeypatch.setenv("INK_K8_TILE", str(mode))
+        S = gpu(dims, dtype, **kw)
+        monkeypatch.delenv("INK_K8_TILE")
+        return S
+    return make
+
+
+@pytest.mark.parametrize("path", parity.GOLDEN, ids=lambda p: p.split("ref_")[-1][:-4])
+def test_gpu_tile_particle_kernel_vs_reference_golden(k8_tile_env, path):
+    """The tile kernel (k_particles_rk2_tile: rows staged by cp.async.bulk, gathers from shared memory) against the COMPILED
+    REFERENCE's particle update, bit for bit: the dense box cloud and the wild cloud (out-of-grid, on-wall, on-face particles:
+    those leave the tile and take the global sampler)."""
+    G = parity.load(path)
+    dims = tuple(int(x) for x in G["dims"])
+    if (dims[2] * 4) % 16 != 0:
+        pytest.skip("rows are not 16-byte multiples: the tile path is not legal here (global-gather kernel runs)")
+    for cloud, dt, kp, kv in (("part", 0.2, "particles_pos", "particles_vel"), ("wild", 0.35, "wild_pos", "wild_vel")):
+        S = k8_tile_env(2, dims)
+        S.set_velocity(G["u"], G["v"], G["w"])
+        S.set_particles(G[cloud])
+        S.particles(dt)
+        pos, vel = S.get_particles()
+        np.testing.assert_array_equal(pos, G[kp]); np.testing.assert_array_equal(vel, G[kv])
+        S.close()
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64], ids=["fp32", "fp64"])
+@pytest.mark.parametrize("arith", ["strict", "fast"])
+def test_gpu_tile_particle_kernel_equals_global_gather_kernel(k8_tile_env, dtype, arith):
+    """Same inputs through both K8 kernels: positions, velocities and the force mask seeded for the next step are identical,
+    bit for bit — uniform and wild clouds, CFL-sized and far too large dt (samples that leave the tile), and many steps
+    without re-binning (particles drift out of the cells they were binned in; the tile follows their bounding box)."""
+    dims = (32, 24, 64)
+    u, v, w = util.rand_field(dims, 51, scale=0.6, dtype=dtype)
+    clouds = {"uniform": util.uniform_particles(dims, 60000, 52, dtype=dtype), "wild": util.wild_particles(dims, 5000, 53, dtype=dtype),
+              "box": util.box_particles(dims, 30000, 54, dtype=dtype)}
+    for name, part in clouds.items():
+        for dt in (0.15, 2.5):
+            A, B = k8_tile_env(2, dims, dtype, arith=arith, resort_interval=1000), k8_tile_env(0, dims, dtype, arith=arith, resort_interval=1000)
+            for T in (A, B):
+                T.set_velocity(u, v, w); T.set_particles(part)
+            for step in range(6):
+                A.particles(dt); B.particles(dt)
+                pa, va = A.get_particles(); pb, vb = B.get_particles()
+                assert np.array_equal(pa, pb) and np.array_equal(va, vb), (name, dt, step)
+            A.forces(0.1); B.forces(0.1)          # consumes the mask K8 seeded from the new positions
+            assert np.array_equal(A.get_mark(), B.get_mark()), (name, dt)
+            A.close(); B.close()
+
+
+def test_gpu_tile_particle_kernel_whole_steps(k8_tile_env, oracle_mod):
+    """Config-2 scene stepped with the tile kernel forced: the step-by-step oracle comparison of
+    test_gpu_full_steps_track_oracle_per_step holds unchanged (re-binning every 4 steps rebuilds the work list)."""
+    dims = util.C2
+    part = util.box_particles(dims, 100000, 1)
+    S = k8_tile_env(2, dims, resort_interval=4)
+    O = oracle_mod.OracleSystem(*dims, dtype=np.float32)
+    for T in (S, O):
+        T.set_particles(part)
+    for step in range(10):
+        assert S.solve(0.35) == O.solve(0.35)
+        po, ps = O.get_particles()[0], S.get_particles()[0]
+        assert np.max(np.abs(ps - po) / np.maximum(np.abs(po), 1.0)) < 1e-6, step
+        S.set_velocity(*O.get_velocity())
+        S.set_particles(po, O.get_particles()[1])
+    S.close()
