@@ -91,6 +91,16 @@ int  ink_set_particles(ink_ctx* c, int drop, const void* pos_xyz, const void* ve
 /* Same, but the caller hands over only THIS rank's particles of the drop (a per-rank loader); identical to
  * ink_set_particles on one GPU. */
 int  ink_set_particles_shard(ink_ctx* c, int drop, const void* pos_xyz, const void* vel_xyz, int64_t n_local, int host_dtype);
+/* Particle seeding ON THE DEVICE.  What is sequential or libm-dependent in the reference's seeders stays with the
+ * caller as small tables; every per-particle operation runs in a kernel, in the reference's expression order, and the particle
+ * arrays never cross PCIe.  Results equal the compiled reference's arrays bit for bit (tests/test_host_cpp.py, -m gpu).
+ * ink_seed_emitter: the 120-radius emitParticleHemisphere scene of System::init (src/system.cpp:18-23, src/inkSolver.cpp:11-42);
+ *   radius[nr] / the azimuth loop values' sinf, cosf [ni] / the polar loop values' sinf, cosf [nj] as the reference's FLOAT loop
+ *   counters produce them; particle (r*ni + i)*nj + j.  ink_seed_box: initParticles (src/system.cpp:62-64,93-115) from the raw
+ *   rand() stream, 3 draws (x, y, z) per particle.  Multi-GPU: every rank passes the full tables / stream, keeps its index shard. */
+int  ink_seed_emitter(ink_ctx* c, int drop, const float* radius, int nr, const float* sin_i, const float* cos_i, int ni,
+                      const float* sin_j, const float* cos_j, int nj);
+int  ink_seed_box(ink_ctx* c, int drop, const int32_t* rand_xyz, int64_t n);
 int  ink_num_drops(const ink_ctx* c);
 int64_t ink_num_particles(const ink_ctx* c, int drop);  /* local shard size under multi-GPU */
 /* getInkParticles() (src/system.cpp:151-153): original particle order; either pointer may be NULL. */

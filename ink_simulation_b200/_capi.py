@@ -46,6 +46,8 @@ SYMBOLS = {
     "ink_sync": (_I, [_VP]),
     "ink_set_particles": (_I, [_VP, _I, _VP, _VP, _L, _I]),
     "ink_set_particles_shard": (_I, [_VP, _I, _VP, _VP, _L, _I]),
+    "ink_seed_emitter": (_I, [_VP, _I, _VP, _I, _VP, _VP, _I, _VP, _VP, _I]),
+    "ink_seed_box": (_I, [_VP, _I, _VP, _L]),
     "ink_num_drops": (_I, [_VP]),
     "ink_num_particles": (_L, [_VP, _I]),
     "ink_get_particles": (_I, [_VP, _I, _VP, _VP, _I]),

@@ -126,6 +126,8 @@ struct CtxBase {
     virtual int sync_io() = 0;
     virtual int phase_ms(float out[8]) = 0;
     virtual int check_finite(int64_t out[2]) = 0;
+    virtual int seed_emitter(int drop, const float* radius, int nr, const float* si, const float* ci, int ni, const float* sj, const float* cj, int nj) = 0;
+    virtual int seed_box(int drop, const int32_t* rnd, int64_t n) = 0;
     virtual int get_phantom(int32_t* have, double v[3]) = 0;
     virtual int set_phantom(int32_t have, const double v[3]) = 0;
 };
@@ -153,6 +155,11 @@ struct Ctx final : CtxBase {
     MgTailArgs mg_tail{};
     size_t mg_tail_smem = 0;
     bool use_mg = false;
+    // INK_MG3_FUSED_DOWN=1: levels >= 1 run k_mg3_down_fused (one launch) instead of the residual + restriction kernel pair.  OFF by
+    // default: measured on B200 (profiles/r2_e_*) the one-pass kernel is SLOWER per level (16.3 / 14.3 / 12.3 us against 11.2 / 9.2 /
+    // 9.1 us for the pair, traced): ~1000 predicated instructions per thread in a grid too small to hide them
+    bool mg_fused_down = false;
+    bool mg_coarsest = true;     // INK_MG3_COARSEST=0: the generic shared-memory tail kernel also when the tail is the coarsest level alone
     bool mg_fuse = true;    // INK_MG3_UNFUSED=1 (debug / A-B): separate residual and full 4x4x4 restriction kernels
     size_t mg_tail_cap = 200 * 1024;   // INK_MG_TAIL_KB: shared-memory budget of the single-block tail (experiments)
     int mg_lc = -1;           // >= 1: levels [mg_lc, mg_lt] run in ONE persistent launch (k_mg3_coarse); -1: per-level kernels
@@ -221,7 +228,12 @@ struct Ctx final : CtxBase {
     unsigned int* tile_nwork = nullptr;
     long long tile_work_cap = 0;
     int tile_chunk = 0;        // > 0: the tile kernel runs with chunks of at most this many slots
-    int tile_mode = 1;         // INK_K8_TILE: 0 off, 1 automatic (dense clouds, 16-byte rows), 2 forced wherever it is legal
+    // INK_K8_TILE: 0 off (default), 1 automatic (dense clouds, 16-byte rows), 2 forced wherever it is legal.  OFF by default:
+    // measured on B200 (profiles/r2_d_*): bit-identical results, but 0.38 ms against 0.24 ms per launch at 10 M particles /
+    // 128x256x128 — a warp's 32 particles span ~53 z-cells of one quarter column, so a shared-memory gather still costs 2.1
+    // wavefronts (bank conflicts between k and k + 32) against 2.6 L1 wavefronts from global memory: 36.5 M vs 39 M in total, no
+    // real saving in the data pipe, while the staging, the bounding-box pass and 3 blocks per SM (56 KB tiles) cost more.
+    int tile_mode = 0;
     // staging for host <-> device conversion
     void* stage = nullptr;
     size_t stage_bytes = 0;
@@ -648,6 +660,54 @@ struct Ctx final : CtxBase {
         seed_valid = false;
         return resort();
     }
+    // ---- seeding on the device: the arrays are produced by a kernel, then handed to set_particles_shard as
+    // device pointers (no PCIe traffic beyond the tables)
+    int seed_emitter(int drop, const float* radius, int nr, const float* si, const float* ci, int ni, const float* sj, const float* cj, int nj) override {
+        if (nr <= 0 || ni <= 0 || nj <= 0) { err = "seed_emitter: empty tables"; return 2; }
+        const long long n = (long long)nr * ni * nj;
+        const long long first = n * rank / world, count = n * (rank + 1) / world - first;
+        const size_t ntab = (size_t)nr + 2 * (size_t)ni + 2 * (size_t)nj;
+        float* tab = nullptr;
+        Real *dpos = nullptr, *dvel = nullptr;
+        CK(cudaMalloc(&tab, ntab * sizeof(float)));
+        CK(cudaMalloc(&dpos, (size_t)std::max<long long>(count, 1) * 3 * sizeof(Real)));
+        CK(cudaMalloc(&dvel, (size_t)std::max<long long>(count, 1) * 3 * sizeof(Real)));
+        float *tr = tab, *tsi = tr + nr, *tci = tsi + ni, *tsj = tci + ni, *tcj = tsj + nj;
+        CK(cudaMemcpyAsync(tr, radius, nr * sizeof(float), cudaMemcpyHostToDevice, stream));
+        CK(cudaMemcpyAsync(tsi, si, ni * sizeof(float), cudaMemcpyHostToDevice, stream));
+        CK(cudaMemcpyAsync(tci, ci, ni * sizeof(float), cudaMemcpyHostToDevice, stream));
+        CK(cudaMemcpyAsync(tsj, sj, nj * sizeof(float), cudaMemcpyHostToDevice, stream));
+        CK(cudaMemcpyAsync(tcj, cj, nj * sizeof(float), cudaMemcpyHostToDevice, stream));
+        const float c = std::cos((float)M_PI);   // the only surviving term of the degenerate rotation (src/inkSolver.cpp:16-18)
+        if (count > 0)
+            LAUNCH((k_seed_emitter<Real>), nblk(count), 256, first, count, ni, nj, (const float*)tr, (const float*)tsi, (const float*)tci, (const float*)tsj,
+                   (const float*)tcj, c, P.X / 2.f, P.Y - 0.1f, P.Z / 2.f, dpos, dvel);
+        CK(cudaGetLastError());
+        CK(cudaStreamSynchronize(stream));
+        const int rc = set_particles_shard(drop, dpos, dvel, count, (int)sizeof(Real) * 8);
+        cudaFree(tab); cudaFree(dpos); cudaFree(dvel);
+        return rc;
+    }
+    int seed_box(int drop, const int32_t* rnd, int64_t n) override {
+        if (n < 0) { err = "seed_box: bad n"; return 2; }
+        const long long first = (long long)n * rank / world, count = (long long)n * (rank + 1) / world - first;
+        int32_t* drnd = nullptr;
+        Real *dpos = nullptr, *dvel = nullptr;
+        CK(cudaMalloc(&drnd, (size_t)std::max<long long>(count, 1) * 3 * sizeof(int32_t)));
+        CK(cudaMalloc(&dpos, (size_t)std::max<long long>(count, 1) * 3 * sizeof(Real)));
+        CK(cudaMalloc(&dvel, (size_t)std::max<long long>(count, 1) * 3 * sizeof(Real)));
+        if (count > 0) {
+            CK(cudaMemcpyAsync(drnd, rnd + 3 * first, (size_t)count * 3 * sizeof(int32_t), cudaMemcpyHostToDevice, stream));
+            // bounds exactly as the reference writes them: float expressions for x and z, double literals for y (src/system.cpp:102-104)
+            LAUNCH((k_seed_box<Real>), nblk(count), 256, count, (const int32_t*)drnd, (double)(P.X / 2.f - P.X / 5.f), (double)(P.X / 2.f + P.X / 5.f),
+                   P.Y - 1.5, P.Y - 1., (double)(P.Z / 2.f - P.Z / 3.f), (double)(P.Z / 2.f + P.Z / 3.f), dpos, dvel);
+        }
+        CK(cudaGetLastError());
+        CK(cudaStreamSynchronize(stream));
+        const int rc = set_particles_shard(drop, dpos, dvel, count, (int)sizeof(Real) * 8);
+        cudaFree(drnd); cudaFree(dpos); cudaFree(dvel);
+        return rc;
+    }
     int num_drops() const override { return (int)drop_n.size(); }
     int64_t num_particles(int drop) const override { return (drop >= 0 && drop < (int)drop_n.size()) ? drop_n[drop] : 0; }
 
@@ -1034,6 +1094,8 @@ struct Ctx final : CtxBase {
         if (const char* e = getenv("INK_TRACE_ITER")) trace_iter = atoi(e);
         if (const char* e = getenv("INK_HOSTTIME")) host_timing = atoi(e) != 0;
         if (const char* e = getenv("INK_NO_GRAPH")) use_graph = (atoi(e) == 0);
+        if (const char* e = getenv("INK_MG3_FUSED_DOWN")) mg_fused_down = atoi(e) != 0;
+        if (const char* e = getenv("INK_MG3_COARSEST")) mg_coarsest = atoi(e) != 0;
         if (const char* e = getenv("INK_MG3_UNFUSED")) mg_fuse = (atoi(e) == 0);
         if (const char* e = getenv("INK_MG_TAIL_KB")) mg_tail_cap = (size_t)std::max(1, atoi(e)) * 1024;
         // measured (B200, 128x256x128): a tail holding only the coarsest (<= 1024-cell) level beats a deeper single-block tail
@@ -1173,6 +1235,11 @@ struct Ctx final : CtxBase {
             const int l_split = mg_lc >= 1 ? mg_lc : mg_lt;   // levels below l_split: one kernel per pass
             for (int l = 0; l < l_split; ++l) {
                 const MgDims &df = lv[l].d, &dc = lv[l + 1].d;
+                if (l >= 1 && mg_fused_down) {    // below the finest level a kernel costs its launch, not its traffic: one launch per level
+                    LAUNCH((k_mg3_down_fused<Real>), mg_blocks(dc), 256, S, df, dc, rhs(l), lv[l + 1].r);
+                    TR(l == 1 ? "down L1" : "down L2+");
+                    continue;
+                }
                 if (df.Z % 4 == 0 && mg_fuse) {   // residual + z-restriction fused (xb holds the half-size z-restricted residual)
                     const long long nv = (long long)df.X * (df.j1 - df.j0) * (df.Z / 4);
                     LAUNCH((k_mg3_residual_rz_v4<Real>), (unsigned int)std::min<long long>(kMgBlocks, std::max<long long>(1, (nv + 255) / 256)), 256, S, df, rhs(l), lv[l].xb);
@@ -1203,7 +1270,9 @@ struct Ctx final : CtxBase {
             } else {
                 const MgDims& d = lv[mg_lt].d;
                 const long long off = (long long)d.j0 * d.X * d.Z;
-                launch_k(k_mg3_tail<Real>, 1, kMgTailThreads, mg_tail_smem, stream, S, mg_tail, rhs(mg_lt) + off, lv[mg_lt].xa + off);
+                if (mg_coarsest && mg_tail.nlev == 1 && !mg_tail.final_dot && (long long)d.X * (d.j1 - d.j0) * d.Z <= kMg3CoarsestCells)
+                    launch_k(k_mg3_coarsest<Real>, 1, kMg3CoarsestThreads, 0, stream, S, d, lv[mg_lt].s, rhs(mg_lt) + off, lv[mg_lt].xa + off);
+                else launch_k(k_mg3_tail<Real>, 1, kMgTailThreads, mg_tail_smem, stream, S, mg_tail, rhs(mg_lt) + off, lv[mg_lt].xa + off);
                 ++stats.kernel_launches;
                 TR("tail");
             }
@@ -1725,6 +1794,10 @@ int ink_commit_positions(ink_ctx* c, int drop) { return c->impl->commit_position
 int ink_fetch_positions_async(ink_ctx* c, int drop, void* pos, int hd) { return c->impl->fetch_positions_async(drop, pos, hd); }
 int ink_sync_io(ink_ctx* c) { return c->impl->sync_io(); }
 
+int ink_seed_emitter(ink_ctx* c, int drop, const float* radius, int nr, const float* sin_i, const float* cos_i, int ni, const float* sin_j, const float* cos_j, int nj) {
+    return c->impl->seed_emitter(drop, radius, nr, sin_i, cos_i, ni, sin_j, cos_j, nj);
+}
+int ink_seed_box(ink_ctx* c, int drop, const int32_t* rand_xyz, int64_t n) { return c->impl->seed_box(drop, rand_xyz, n); }
 int ink_check_finite(ink_ctx* c, int64_t out[2]) { return c->impl->check_finite(out); }
 int ink_get_phantom(ink_ctx* c, int32_t* have, double v[3]) { return c->impl->get_phantom(have, v); }
 int ink_set_phantom(ink_ctx* c, int32_t have, const double v[3]) { return c->impl->set_phantom(have, v); }

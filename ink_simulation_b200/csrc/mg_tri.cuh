@@ -71,6 +71,62 @@ INK_HD void mg3_restrict(const MgDims& df, const MgDims& dc, const Real* __restr
     }
 }
 
+// ---- down pass in ONE operator: rc = P^T (r - (omega/6) M r) without storing the residual ------------------------------
+// With res = (1-omega) r + (omega/6) N r (N = sum of the in-grid face neighbours) and the separable restriction weights
+// a = (0, 1/4, 3/4, 3/4, 1/4, 0) on the fine positions 2I-2 .. 2I+3 of each axis (zero where the fine cell does not exist),
+//     rc[I,J,K] = sum_n r_n [ (1-omega) ax ay az + (omega/6) (bx ay az + ax by az + ax ay bz) ],   b[p] = a[p-1] + a[p+1]
+// (b zero where the fine cell n does not exist: N only sums existing neighbours).  Per (x, y) column of the 6x6 window two
+// z-contractions (with az over 4 cells, with bz over 6) — 160 loads per coarse cell instead of a stored residual and a second
+// kernel.  Used on the levels below the finest, where a kernel costs its launch latency, not its traffic.
+template <class Real>
+INK_HD void mg3_axis_weights(int f0, int lo, int hi, Real (&a)[6], Real (&b)[6]) {   // f0 = fine index of position 0 (= 2 I - 2)
+    const Real w[6] = {Real(0), Real(0.25), Real(0.75), Real(0.75), Real(0.25), Real(0)};
+    Real am[8];
+    am[0] = Real(0); am[7] = Real(0);
+#pragma unroll
+    for (int p = 0; p < 6; ++p) { const int f = f0 + p; a[p] = (f >= lo && f < hi) ? w[p] : Real(0); am[p + 1] = a[p]; }
+#pragma unroll
+    for (int p = 0; p < 6; ++p) { const int f = f0 + p; b[p] = (f >= lo && f < hi) ? am[p] + am[p + 2] : Real(0); }
+}
+template <class Real>
+INK_HD void mg3_down_fused(const MgDims& df, const MgDims& dc, const Real* __restrict__ r, Real* __restrict__ rc, long long tid, long long nth) {
+    const Real c0 = Real(1) - Real(kMgOmega), c1 = Real(kMgOmega) / Real(6);
+    INK_MG_CELL_LOOP(dc, tid, nth) {
+        INK_MG_DECODE(dc)
+        Real ax[6], bx[6], ay[6], by[6], az[6], bz[6];
+        mg3_axis_weights<Real>(2 * i - 2, 0, df.X, ax, bx);
+        mg3_axis_weights<Real>(2 * j - 2, df.j0, df.j1, ay, by);
+        mg3_axis_weights<Real>(2 * k - 2, 0, df.Z, az, bz);
+        const int fk0 = 2 * k - 2;
+        Real acc = Real(0);
+#pragma unroll
+        for (int py = 0; py < 6; ++py)
+#pragma unroll
+            for (int px = 0; px < 6; ++px) {
+                const bool ox = (px == 0 || px == 5), oy = (py == 0 || py == 5);
+                if (ox && oy) continue;                                   // both weights vanish identically
+                const Real wa = c0 * (ax[px] * ay[py]) + c1 * (bx[px] * ay[py] + ax[px] * by[py]);
+                const Real wb = c1 * (ax[px] * ay[py]);
+                if (wa == Real(0) && wb == Real(0)) continue;             // column outside the grid / slab
+                const Real* __restrict__ row = r + mg_idx(df, 2 * i - 2 + px, 2 * j - 2 + py, 0);
+                Real v[6];
+#pragma unroll
+                for (int pz = 0; pz < 6; ++pz) {
+                    const int fk = fk0 + pz;
+                    const bool need = (pz >= 1 && pz <= 4) || !(ox || oy);   // the outer z positions only enter through bz
+                    v[pz] = (need && fk >= 0 && fk < df.Z) ? row[fk] : Real(0);
+                }
+                const Real sa = (az[1] * v[1] + az[2] * v[2]) + (az[3] * v[3] + az[4] * v[4]);
+                acc += wa * sa;
+                if (!(ox || oy)) {
+                    const Real sb = ((bz[0] * v[0] + bz[1] * v[1]) + (bz[2] * v[2] + bz[3] * v[3])) + (bz[4] * v[4] + bz[5] * v[5]);
+                    acc += wb * sb;
+                }
+            }
+        rc[c] = acc;
+    }
+}
+
 // the four fine positions 2c-1, 2c, 2c+1, 2c+2 interpolated from coarse c-1, c, c+1
 template <class Real>
 INK_HD void mg3_interp4(Real v0, Real v1, Real v2, Real (&o)[4]) {
@@ -433,6 +489,74 @@ __global__ void __launch_bounds__(256) k_mg3_restrict_xy_v4(const CgScal* S, MgD
     INK_PDL();
     if (S->done) return;
     mg3_restrict_xy_v4_dev<Real>(df, dc, resz, rc, blockIdx.x * blockDim.x + threadIdx.x, gridDim.x * blockDim.x);
+}
+
+template <class Real>
+__global__ void __launch_bounds__(256) k_mg3_down_fused(const CgScal* S, MgDims df, MgDims dc, const Real* __restrict__ r, Real* __restrict__ rc) {
+    INK_PDL();
+    if (S->done) return;
+    mg3_down_fused<Real>(df, dc, r, rc, (long long)blockIdx.x * blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x);
+}
+
+// ---- the coarsest level alone (<= kMg3CoarsestCells cells): kMgCoarsestSweeps damped-Jacobi sweeps from zero ----------------
+// One block, up to 2 cells per thread, state in shared memory, the six neighbour slots resolved ONCE (a missing neighbour points
+// at a zero slot): a sweep is 7 shared loads, 8 flops and a barrier.  Same expressions in the same order as mg_smooth (the
+// generic tail, k_mg3_tail, took 11.5 us of every ~115 us PCG iteration for this: strided iterators, predicated neighbour sums
+// and 308 bytes of spills under its 64-register cap).
+constexpr int kMg3CoarsestThreads = 1024;
+template <class Real>
+__global__ void __launch_bounds__(kMg3CoarsestThreads) k_mg3_coarsest(const CgScal* S, MgDims d, Real s, const Real* __restrict__ rin, Real* __restrict__ xout) {
+    INK_PDL();
+    if (S->done) return;
+    __shared__ Real xs[2][kMg3CoarsestCells + 1];
+    const int X = d.X, Z = d.Z, rows = d.j1 - d.j0, n = X * rows * Z;   // rin / xout already point at the slab's first cell
+    const Real cj = Real(kMgOmega) / (Real(6) * s);
+    int nb[2][6];
+    Real rr[2], xc[2];
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+        const int c = threadIdx.x + q * kMg3CoarsestThreads;
+        rr[q] = Real(0); xc[q] = Real(0);
+#pragma unroll
+        for (int a = 0; a < 6; ++a) nb[q][a] = n;
+        if (c < n) {
+            const int k = c % Z, row = c / Z, i = row % X, jl = row / X;
+            if (i + 1 < X) nb[q][0] = c + Z;
+            if (i > 0) nb[q][1] = c - Z;
+            if (jl + 1 < rows) nb[q][2] = c + X * Z;
+            if (jl > 0) nb[q][3] = c - X * Z;
+            if (k + 1 < Z) nb[q][4] = c + 1;
+            if (k > 0) nb[q][5] = c - 1;
+            rr[q] = rin[c];
+            xc[q] = cj * rr[q];
+            xs[0][c] = xc[q];
+        }
+    }
+    if (threadIdx.x == 0) { xs[0][n] = Real(0); xs[1][n] = Real(0); }
+    __syncthreads();
+    int cur = 0;
+    for (int t = 1; t < kMgCoarsestSweeps; ++t) {
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            const int c = threadIdx.x + q * kMg3CoarsestThreads;
+            if (c < n) {
+                const Real* x = xs[cur];
+                Real a = Real(0);
+#pragma unroll
+                for (int e = 0; e < 6; ++e) a += x[nb[q][e]];
+                const Real Lx = Real(6) * xc[q] - a;
+                xc[q] = xc[q] + cj * (rr[q] - s * Lx);
+                xs[cur ^ 1][c] = xc[q];
+            }
+        }
+        __syncthreads();
+        cur ^= 1;
+    }
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+        const int c = threadIdx.x + q * kMg3CoarsestThreads;
+        if (c < n) xout[c] = xc[q];
+    }
 }
 
 // ---- shared-memory tail: all levels from `lt` down in ONE block (MgTailArgs of mg.cuh; 3 arrays per level) ----------

@@ -261,6 +261,53 @@ __global__ void __launch_bounds__(256) k_sample(Grid g, Consts<Real> C, long lon
 }
 
 // ------------------------------------------------------------------------------------------------
+// Particle seeding ON THE DEVICE.  The reference seeds on the host with FLOAT loop counters and glibc's
+// sinf / cosf / rand(); what is sequential or libm-dependent (the accumulated loop values, their sines and cosines, the raw
+// rand() stream) comes in as small tables, every per-particle operation happens here, in the reference's float / double
+// expression order (no FMA contraction in this translation unit), so the arrays equal the compiled reference's bit for bit.
+// ------------------------------------------------------------------------------------------------
+// emitParticleHemisphere for all radii (src/inkSolver.cpp:11-42 called from src/system.cpp:18-23): particle
+// n = (r * ni + i) * nj + j.  The rotation AngleAxisf(pi, (n + up).normalized()) is about the ZERO axis and degenerates to
+// cos(pi) * I: velocity = c * (x, y, z) with the zero terms of the 3x3 product kept (sign of zero), position =
+// ceiling centre + radius * velocity.  Writes AoS xyz of particles [first, first + count).
+template <class Real>
+__global__ void __launch_bounds__(256) k_seed_emitter(long long first, long long count, int ni, int nj, const float* __restrict__ radius,
+                                                      const float* __restrict__ sin_i, const float* __restrict__ cos_i, const float* __restrict__ sin_j,
+                                                      const float* __restrict__ cos_j, float c, float cx, float cy, float cz, Real* __restrict__ pos,
+                                                      Real* __restrict__ vel) {
+    INK_PDL();
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= count) return;
+    const long long n = first + t;
+    const int j = (int)(n % nj);
+    const long long q = n / nj;
+    const int i = (int)(q % ni), r = (int)(q / ni);
+    const float rad = radius[r];
+    const float x = rad * sin_j[j] * sin_i[i];
+    const float y = rad * cos_j[j];
+    const float z = rad * sin_j[j] * cos_i[i];
+    const float zf = 0.f;
+    const float vx = (c * x + zf * y) + zf * z, vy = (zf * x + c * y) + zf * z, vz = (zf * x + zf * y) + c * z;
+    pos[3 * t] = (Real)(cx + rad * vx); pos[3 * t + 1] = (Real)(cy + rad * vy); pos[3 * t + 2] = (Real)(cz + rad * vz);
+    vel[3 * t] = (Real)vx; vel[3 * t + 1] = (Real)vy; vel[3 * t + 2] = (Real)vz;
+}
+// initParticles (src/system.cpp:62-64, 93-115): position = float(lo + (double(rand()) / RAND_MAX) * (hi - lo)) per axis, draw
+// order x, y, z; rnd holds the caller's rand() stream, 3 draws per particle.
+template <class Real>
+__global__ void __launch_bounds__(256) k_seed_box(long long count, const int32_t* __restrict__ rnd, double lox, double hix, double loy, double hiy,
+                                                  double loz, double hiz, Real* __restrict__ pos, Real* __restrict__ vel) {
+    INK_PDL();
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= count) return;
+    const double rmax = 2147483647.0;   // RAND_MAX of glibc
+    const float x = (float)(lox + ((double)rnd[3 * t] / rmax) * (hix - lox));
+    const float y = (float)(loy + ((double)rnd[3 * t + 1] / rmax) * (hiy - loy));
+    const float z = (float)(loz + ((double)rnd[3 * t + 2] / rmax) * (hiz - loz));
+    pos[3 * t] = (Real)x; pos[3 * t + 1] = (Real)y; pos[3 * t + 2] = (Real)z;
+    vel[3 * t] = Real(0); vel[3 * t + 1] = Real(0); vel[3 * t + 2] = Real(0);
+}
+
+// ------------------------------------------------------------------------------------------------
 // Import / export (AoS xyz in the caller's dtype <-> internal SoA) and cell binning.
 // ------------------------------------------------------------------------------------------------
 template <class Tin, class Real>

@@ -83,6 +83,17 @@ void hemisphere(int X, int Y, int Z, float radius, std::vector<Particle>& out) {
     }
 }
 
+// The loop-variable tables of the emitter scene for ink_seed_emitter (device seeding): the float loop counters of System::init
+// (src/system.cpp:18-23) and emitParticleHemisphere (src/inkSolver.cpp:13-14,19-20) and glibc's sinf / cosf of them — the only
+// parts of the seeder that are sequential or libm-dependent; the per-particle products run on the GPU.
+void emitter_tables(std::vector<float>& radius, std::vector<float>& sin_i, std::vector<float>& cos_i, std::vector<float>& sin_j, std::vector<float>& cos_j) {
+    const float fraction = M_PI / 36.f;
+    const float twoPi = M_PI * 2.f;
+    for (float i = 0; i < 2 * M_PI; i += (M_PI / 60.f)) radius.push_back(i);
+    for (float i = 0; i < twoPi; i += fraction) { sin_i.push_back(std::sin(i)); cos_i.push_back(std::cos(i)); }
+    for (float j = 0; j < M_PI; j += fraction) { sin_j.push_back(std::sin(j)); cos_j.push_back(std::cos(j)); }
+}
+
 void emitter_scene(int X, int Y, int Z, std::vector<Particle>& out) {
     for (float i = 0; i < 2 * M_PI; i += (M_PI / 60.f)) hemisphere(X, Y, Z, i, out);
 }
@@ -120,4 +131,18 @@ extern "C" long inkhost_from_file(const char* path, float* pos, float* vel, long
             for (int a = 0; a < 3; ++a) { pos[3 * i + a] = ink[i].position[a]; vel[3 * i + a] = ink[i].velocity[a]; }
         return n;
     } catch (const std::exception&) { return -1; }
+}
+
+// device seeding (ink_seed_emitter / ink_seed_box): the tables and the rand() stream the Python host hands to the C ABI
+extern "C" void inkhost_emitter_tables(float* radius, int* nr, float* sin_i, float* cos_i, int* ni, float* sin_j, float* cos_j, int* nj, int cap) {
+    std::vector<float> r, si, ci, sj, cj;
+    inkseed::emitter_tables(r, si, ci, sj, cj);
+    *nr = (int)r.size(); *ni = (int)si.size(); *nj = (int)sj.size();
+    for (int a = 0; a < *nr && a < cap; ++a) radius[a] = r[a];
+    for (int a = 0; a < *ni && a < cap; ++a) { sin_i[a] = si[a]; cos_i[a] = ci[a]; }
+    for (int a = 0; a < *nj && a < cap; ++a) { sin_j[a] = sj[a]; cos_j[a] = cj[a]; }
+}
+extern "C" void inkhost_rand_stream(int32_t* out, long n) {   // a fresh process's rand() sequence (the reference never seeds it)
+    std::srand(1);
+    for (long a = 0; a < n; ++a) out[a] = rand();
 }

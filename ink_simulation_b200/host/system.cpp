@@ -39,17 +39,42 @@ void System::init() {
     if (const char* e = std::getenv("INK_DEVICE")) p.device = std::atoi(e);
     if (ink_create(&p, &m_ctx) != 0) throw std::runtime_error(std::string("ink_create: ") + ink_last_error(nullptr));
 
+    // Particle seeding.  The emitter scene and the initParticles box are produced ON THE DEVICE (ink_seed_emitter /
+    // ink_seed_box): the host only supplies the float loop counters with their sinf / cosf, or the rand() stream.
+    // INK_SEED_ON_HOST=1 keeps the host seeders (seeding.cpp, the code the CPU tests pin to the compiled reference) + one upload.
+    const bool on_host = std::getenv("INK_SEED_ON_HOST") && std::atoi(std::getenv("INK_SEED_ON_HOST")) != 0;
+    Particle blank;
+    blank.position = blank.velocity = Vector3f(0, 0, 0);
+    blank.opacity = 1.f;
+    blank.lifeTime = 5.f;
     if (PART_FILE != "") {
         initFromFile();
+        uploadInk();
     } else if (INK_SEED_BOX) {
-        initParticles();
+        if (on_host) { initParticles(); uploadInk(); return; }
+        for (size_t d = 0; d < NUM_PARTICLES.size(); ++d) {   // src/system.cpp:62-64: rand() is drawn x, y, z per particle, drop after drop
+            std::vector<int32_t> rnd(3 * (size_t)NUM_PARTICLES[d]);
+            for (auto& v : rnd) v = rand();
+            if (ink_seed_box(m_ctx, (int)d, rnd.data(), (int64_t)NUM_PARTICLES[d]) != 0) fail("ink_seed_box");
+            m_ink.emplace_back((size_t)NUM_PARTICLES[d], blank);
+        }
+        m_inkStale = true;   // the mirror is filled from the device by the first getInkParticles()
     } else {
-        std::vector<Particle> ink;
-        ink.reserve(400000);
-        m_ink.push_back(ink);
-        for (float i = 0; i < 2 * M_PI; i += (M_PI / 60.f)) emitParticleHemisphere(i);
+        if (on_host) {
+            std::vector<Particle> ink;
+            ink.reserve(400000);
+            m_ink.push_back(ink);
+            for (float i = 0; i < 2 * M_PI; i += (M_PI / 60.f)) emitParticleHemisphere(i);
+            uploadInk();
+            return;
+        }
+        std::vector<float> radius, si, ci, sj, cj;
+        inkseed::emitter_tables(radius, si, ci, sj, cj);
+        if (ink_seed_emitter(m_ctx, 0, radius.data(), (int)radius.size(), si.data(), ci.data(), (int)si.size(), sj.data(), cj.data(), (int)sj.size()) != 0)
+            fail("ink_seed_emitter");
+        m_ink.emplace_back(radius.size() * si.size() * sj.size(), blank);
+        m_inkStale = true;
     }
-    uploadInk();
 }
 
 void System::uploadInk() {

@@ -54,3 +54,36 @@ def from_file(path):
     pos, vel = np.empty((n, 3), np.float32), np.empty((n, 3), np.float32)
     L.inkhost_from_file(str(path).encode(), _vp(pos), _vp(vel), C.c_long(n))
     return pos, vel
+
+
+# ---- device seeding (ink_seed_emitter / ink_seed_box): the host supplies only what is sequential or libm-dependent ----------
+def emitter_tables():
+    """(radius, sin_i, cos_i, sin_j, cos_j): the float loop counters of the emitter scene and glibc's sinf / cosf of them"""
+    cap = 256
+    arrs = [np.empty(cap, np.float32) for _ in range(5)]
+    nr, ni, nj = C.c_int(), C.c_int(), C.c_int()
+    host_lib().inkhost_emitter_tables(_vp(arrs[0]), C.byref(nr), _vp(arrs[1]), _vp(arrs[2]), C.byref(ni), _vp(arrs[3]), _vp(arrs[4]), C.byref(nj),
+                                      C.c_int(cap))
+    assert max(nr.value, ni.value, nj.value) <= cap
+    return (arrs[0][:nr.value].copy(), arrs[1][:ni.value].copy(), arrs[2][:ni.value].copy(), arrs[3][:nj.value].copy(), arrs[4][:nj.value].copy())
+
+
+def rand_stream(n):
+    """the first n draws of glibc's unseeded rand() (what initParticles consumes: x, y, z per particle)"""
+    out = np.empty(n, np.int32)
+    host_lib().inkhost_rand_stream(_vp(out), C.c_long(n))
+    return out
+
+
+def seed_emitter_on_device(system, drop=0):
+    """System::init's emitter scene produced by a kernel (ink_seed_emitter); returns the particle count"""
+    r, si, ci, sj, cj = emitter_tables()
+    system._ck(system.L.ink_seed_emitter(system.h, drop, _vp(r), len(r), _vp(si), _vp(ci), len(si), _vp(sj), _vp(cj), len(sj)))
+    return len(r) * len(si) * len(sj)
+
+
+def seed_box_on_device(system, n, drop=0, stream=None):
+    """initParticles produced by a kernel (ink_seed_box) from the rand() stream"""
+    rnd = rand_stream(3 * n) if stream is None else np.ascontiguousarray(stream, np.int32)
+    system._ck(system.L.ink_seed_box(system.h, drop, _vp(rnd), n))
+    return n

@@ -29,9 +29,14 @@ static int run(MgDims d0, int T, const char* in, const char* out) {
     if (!f || fread(r[0].data(), sizeof(Real), r[0].size(), f) != r[0].size()) { fprintf(stderr, "cannot read %s\n", in); return 2; }
     fclose(f);
     Real s = 1;
+    const bool fused = getenv("MG_HARNESS_FUSED") && atoi(getenv("MG_HARNESS_FUSED")) != 0;   // the one-pass down operator (levels >= 1 on the GPU)
     for (int l = 0; l + 1 < L; ++l) {
-        for (int tid = 0; tid < T; ++tid) mg3_residual<Real>(d[l], r[l].data(), t[l].data(), tid, T);
-        for (int tid = 0; tid < T; ++tid) mg3_restrict<Real>(d[l], d[l + 1], t[l].data(), r[l + 1].data(), tid, T);
+        if (fused) {
+            for (int tid = 0; tid < T; ++tid) mg3_down_fused<Real>(d[l], d[l + 1], r[l].data(), r[l + 1].data(), tid, T);
+        } else {
+            for (int tid = 0; tid < T; ++tid) mg3_residual<Real>(d[l], r[l].data(), t[l].data(), tid, T);
+            for (int tid = 0; tid < T; ++tid) mg3_restrict<Real>(d[l], d[l + 1], t[l].data(), r[l + 1].data(), tid, T);
+        }
         s *= 2;
     }
     {
