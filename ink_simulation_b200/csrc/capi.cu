@@ -159,6 +159,7 @@ struct Ctx final : CtxBase {
     // default: measured on B200 (profiles/r2_e_*) the one-pass kernel is SLOWER per level (16.3 / 14.3 / 12.3 us against 11.2 / 9.2 /
     // 9.1 us for the pair, traced): ~1000 predicated instructions per thread in a grid too small to hide them
     bool mg_fused_down = false;
+    int mg_up_tile = 1;          // INK_MG3_UP_TILE: 0 = k_mg3_up everywhere, 1 = k_mg3_up_tile on levels with >= 2 tiles per SM, 2 = wherever legal
     bool mg_coarsest = true;     // INK_MG3_COARSEST=0: the generic shared-memory tail kernel also when the tail is the coarsest level alone
     bool mg_fuse = true;    // INK_MG3_UNFUSED=1 (debug / A-B): separate residual and full 4x4x4 restriction kernels
     size_t mg_tail_cap = 200 * 1024;   // INK_MG_TAIL_KB: shared-memory budget of the single-block tail (experiments)
@@ -1096,6 +1097,9 @@ struct Ctx final : CtxBase {
         if (const char* e = getenv("INK_NO_GRAPH")) use_graph = (atoi(e) == 0);
         if (const char* e = getenv("INK_MG3_FUSED_DOWN")) mg_fused_down = atoi(e) != 0;
         if (const char* e = getenv("INK_MG3_COARSEST")) mg_coarsest = atoi(e) != 0;
+        if (const char* e = getenv("INK_MG3_UP_TILE")) mg_up_tile = atoi(e);
+        CK(cudaFuncSetAttribute((k_mg3_up_tile<Real, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mg3_up_tile_smem<Real>()));
+        CK(cudaFuncSetAttribute((k_mg3_up_tile<Real, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mg3_up_tile_smem<Real>()));
         if (const char* e = getenv("INK_MG3_UNFUSED")) mg_fuse = (atoi(e) == 0);
         if (const char* e = getenv("INK_MG_TAIL_KB")) mg_tail_cap = (size_t)std::max(1, atoi(e)) * 1024;
         // measured (B200, 128x256x128): a tail holding only the coarsest (<= 1024-cell) level beats a deeper single-block tail
@@ -1282,7 +1286,16 @@ struct Ctx final : CtxBase {
                 // block_sum_last cap the FINAL launch at kCgMaxBlocks blocks
                 const long long ncc = (long long)dc.X * (dc.j1 - dc.j0) * dc.Z;
                 const unsigned int ub = (unsigned int)std::max<long long>(1, (ncc + 255) / 256);
-                if (l == 0) LAUNCH((k_mg3_up<Real, true>), std::min<unsigned int>(ub, kCgMaxBlocks), 256, S, df, dc, lv[l].s, rhs(l), lv[l + 1].xa, lv[l].xa, dot0, dot1);
+                // levels with enough tiles to fill the GPU: the shared-memory tile version (38 instead of 85 instructions per fine cell)
+                const int ntx = (df.X + kUpTX - 1) / kUpTX, nty = (df.j1 - (df.j0 & ~1) + kUpTY - 1) / kUpTY, ntz = (df.Z + kUpTZ - 1) / kUpTZ;
+                const long long ntile = (long long)ntx * nty * ntz;
+                if (mg_up_tile && df.Z % 4 == 0 && (long long)df.X * df.Y * df.Z < (1ll << 31) && ntile >= (mg_up_tile == 2 ? 1 : 2 * kSMs)) {
+                    const unsigned int nb = (unsigned int)std::min<long long>(ntile, kCgMaxBlocks);
+                    if (l == 0) launch_k((k_mg3_up_tile<Real, true>), nb, 256, mg3_up_tile_smem<Real>(), stream, S, df, dc, lv[l].s, rhs(l), (const Real*)lv[l + 1].xa, lv[l].xa, dot0, dot1, ntx, nty, ntz);
+                    else launch_k((k_mg3_up_tile<Real, false>), nb, 256, mg3_up_tile_smem<Real>(), stream, S, df, dc, lv[l].s, rhs(l), (const Real*)lv[l + 1].xa, lv[l].xa, 0, 0, ntx, nty, ntz);
+                    ++stats.kernel_launches;
+                }
+                else if (l == 0) LAUNCH((k_mg3_up<Real, true>), std::min<unsigned int>(ub, kCgMaxBlocks), 256, S, df, dc, lv[l].s, rhs(l), lv[l + 1].xa, lv[l].xa, dot0, dot1);
                 else LAUNCH((k_mg3_up<Real, false>), ub, 256, S, df, dc, lv[l].s, rhs(l), lv[l + 1].xa, lv[l].xa, 0, 0);
                 TR(l == 0 ? "up L0" : l == 1 ? "up L1" : "up L2+");
             }

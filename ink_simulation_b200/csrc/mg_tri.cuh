@@ -379,6 +379,144 @@ __global__ void __launch_bounds__(256, 3) k_mg3_up(CgScal* S, MgDims df, MgDims 
     }
 }
 
+// ---- up pass through a shared-memory tile (the finest levels) ----------------------------------------------------------------
+// k_mg3_up gives one thread a coarse cell and lets it form x' = c r + P e on the whole 4x4x4 fine neighbourhood of its 2x2x2
+// block: every x' is computed 4 times, ~680 warp instructions per coarse-cell warp, 80 registers, 39 % issue utilisation — the
+// largest single kernel of a PCG iteration (33 us of ~110 at 128x256x128, 92 us of 340 at 256^3: 1.2-1.5 TB/s for 8.5 B/cell).
+// Here a block owns a kUpTX x kUpTY x kUpTZ fine tile:
+//   stage  the (TX/2+2)(TY/2+2)(TZ/2+2) coarse values around it in shared memory (zero outside the coarse grid / slab),
+//   A      x' = c r + P e for the tile plus a one-cell halo, four z-consecutive cells per thread (separable: 28 FMAs per
+//          quad from 16 shared coarse values, one LDG.128 of r), into shared memory — each x' once (1.6x with the halo),
+//   B      z = c r + (1-omega) x' + (omega/6) N x' from shared memory (5 LDS.128 + 2 LDS.32 per quad), one STG.128, <r,z>.
+// ~38 instructions per fine cell instead of ~85.  Same operator as mg3_up (cells outside the grid / slab hold x' = 0, which is
+// "N sums existing neighbours only"); different rounding order.  Z % 4 == 0 (vector accesses); any X, Y, slab start.
+constexpr int kUpTX = 8, kUpTY = 8, kUpTZ = 64;
+constexpr int kUpRows = (kUpTX + 2) * (kUpTY + 2);       // fine rows of the tile + halo
+constexpr int kUpRow = kUpTZ + 8;                        // [3 pad][k = -1][TZ cells][k = TZ][3 pad]: cell k at 4 + k, 16-byte aligned quads
+constexpr int kUpCX = kUpTX / 2 + 2, kUpCY = kUpTY / 2 + 2, kUpCZ = kUpTZ / 2 + 2;
+constexpr int kUpCRow = kUpCZ + 2;                       // even row length: 8-byte aligned pairs
+template <class Real>
+constexpr size_t mg3_up_tile_smem() { return (size_t)(kUpRows * kUpRow + kUpCX * kUpCY * kUpCRow) * sizeof(Real); }
+
+// (3 * main + other) donors of fine index f on one axis, as local indices into the staged coarse tile whose origin is c0
+__device__ __forceinline__ void mg3_donors(int f, int c0, int& pm, int& po) {
+    const int c = f >> 1;
+    pm = c - c0;
+    po = pm + ((f & 1) ? 1 : -1);
+}
+
+template <class Real, bool FINAL>
+__global__ void __launch_bounds__(256) k_mg3_up_tile(CgScal* S, MgDims df, MgDims dc, Real s, const Real* __restrict__ r, const Real* __restrict__ e,
+                                                     Real* __restrict__ z, int dj0, int dj1, int ntx, int nty, int ntz) {
+    INK_PDL();
+    if (S->done) return;
+    extern __shared__ __align__(16) unsigned char up_smem_raw[];
+    Real* xs = reinterpret_cast<Real*>(up_smem_raw);            // x' rows
+    Real* es = xs + kUpRows * kUpRow;                           // coarse values
+    const Real cj = Real(kMgOmega) / (Real(6) * s), a0 = Real(1) - Real(kMgOmega), a1 = Real(kMgOmega) / Real(6), sc = Real(1) / Real(64);
+    const int tid = threadIdx.x;
+    const int jbase = df.j0 & ~1;                               // tiles start on even rows so that a tile's coarse origin is fy0 / 2 - 1
+    const int sxf = df.Z, syf = df.X * df.Z;                    // 32-bit element strides (a level has < 2^31 cells)
+    double acc = 0;
+    for (int tile = blockIdx.x; tile < ntx * nty * ntz; tile += gridDim.x) {
+        const int tz_ = tile % ntz, txy = tile / ntz, tx_ = txy % ntx, ty_ = txy / ntx;
+        const int fx0 = tx_ * kUpTX, fy0 = jbase + ty_ * kUpTY, fz0 = tz_ * kUpTZ;
+        const int cx0 = (fx0 >> 1) - 1, cy0 = (fy0 >> 1) - 1, cz0 = (fz0 >> 1) - 1;
+        // ---- stage the coarse values (zero outside the coarse grid / slab: dropped donors)
+        for (int q = tid; q < kUpCX * kUpCY * kUpCZ; q += 256) {
+            const int kk = q % kUpCZ, col = q / kUpCZ, ci = cx0 + col % kUpCX, cjj = cy0 + col / kUpCX, ck = cz0 + kk;
+            const bool ok = ci >= 0 && ci < dc.X && cjj >= dc.j0 && cjj < dc.j1 && ck >= 0 && ck < dc.Z;
+            es[col * kUpCRow + kk] = ok ? e[((long long)cjj * dc.X + ci) * dc.Z + ck] : Real(0);
+        }
+        __syncthreads();
+        // ---- A: x' on the tile + halo rows, one z-quad per thread and pass
+        for (int q = tid; q < kUpRows * (kUpTZ / 4); q += 256) {
+            const int zq = q % (kUpTZ / 4), row = q / (kUpTZ / 4), lx = row % (kUpTX + 2), ly = row / (kUpTX + 2);
+            const int fi = fx0 - 1 + lx, fj = fy0 - 1 + ly, fk = fz0 + 4 * zq;
+            P4<Real> xp = p4_zero<Real>();
+            if (fi >= 0 && fi < df.X && fj >= df.j0 && fj < df.j1 && fk < df.Z) {
+                const P4<Real> rq = ldp<Real, 4>(r + (fj * syf + fi * sxf + fk));
+                int xm, xo, ym, yo;
+                mg3_donors(fi, cx0, xm, xo);
+                mg3_donors(fj, cy0, ym, yo);
+                const int lk = 2 * zq;                           // local coarse index of K - 1, K = fk / 2
+                Real t[2][2][4];                                 // [x donor][y donor][fine cell]: z-interpolated columns
+#pragma unroll
+                for (int a = 0; a < 2; ++a)
+#pragma unroll
+                    for (int b = 0; b < 2; ++b) {
+                        const Real* col = es + ((b ? yo : ym) * kUpCX + (a ? xo : xm)) * kUpCRow + lk;
+                        const Pack<Real, 2> v01 = ldp<Real, 2>(col), v23 = ldp<Real, 2>(col + 2);
+                        t[a][b][0] = hd_fma(Real(3), v01.a[1], v01.a[0]);
+                        t[a][b][1] = hd_fma(Real(3), v01.a[1], v23.a[0]);
+                        t[a][b][2] = hd_fma(Real(3), v23.a[0], v01.a[1]);
+                        t[a][b][3] = hd_fma(Real(3), v23.a[0], v23.a[1]);
+                    }
+#pragma unroll
+                for (int m = 0; m < 4; ++m) {
+                    const Real um = hd_fma(Real(3), t[0][0][m], t[0][1][m]);   // main x donor: 3 * main y + other y
+                    const Real uo = hd_fma(Real(3), t[1][0][m], t[1][1][m]);
+                    xp.a[m] = hd_fma(sc, hd_fma(Real(3), um, uo), cj * rq.a[m]);
+                }
+            }
+            stp<Real, 4>(xs + row * kUpRow + 4 + 4 * zq, xp);
+        }
+        // the two z-halo cells (k = fz0 - 1, fz0 + TZ) of the INTERIOR rows
+        for (int q = tid; q < kUpTX * kUpTY * 2; q += 256) {
+            const int side = q & 1, col = q >> 1, lx = 1 + col % kUpTX, ly = 1 + col / kUpTX;
+            const int fi = fx0 - 1 + lx, fj = fy0 - 1 + ly, fk = side ? fz0 + kUpTZ : fz0 - 1;
+            Real v = Real(0);
+            if (fi < df.X && fj >= df.j0 && fj < df.j1 && fk >= 0 && fk < df.Z) {
+                int xm, xo, ym, yo, zm, zo;
+                mg3_donors(fi, cx0, xm, xo);
+                mg3_donors(fj, cy0, ym, yo);
+                mg3_donors(fk, cz0, zm, zo);
+                Real u2[2];
+#pragma unroll
+                for (int a = 0; a < 2; ++a) {
+                    const Real* c0 = es + (ym * kUpCX + (a ? xo : xm)) * kUpCRow;
+                    const Real* c1 = es + (yo * kUpCX + (a ? xo : xm)) * kUpCRow;
+                    u2[a] = hd_fma(Real(3), hd_fma(Real(3), c0[zm], c0[zo]), hd_fma(Real(3), c1[zm], c1[zo]));
+                }
+                v = hd_fma(sc, hd_fma(Real(3), u2[0], u2[1]), cj * r[fj * syf + fi * sxf + fk]);
+            }
+            xs[(ly * (kUpTX + 2) + lx) * kUpRow + (side ? 4 + kUpTZ : 3)] = v;
+        }
+        __syncthreads();
+        // ---- B: z = c r + (1 - omega) x' + (omega / 6) N x' on the tile
+        for (int q = tid; q < kUpTX * kUpTY * (kUpTZ / 4); q += 256) {
+            const int zq = q % (kUpTZ / 4), col = q / (kUpTZ / 4), lx = 1 + col % kUpTX, ly = 1 + col / kUpTX;
+            const int fi = fx0 - 1 + lx, fj = fy0 - 1 + ly, fk = fz0 + 4 * zq;
+            if (fi >= df.X || fj < df.j0 || fj >= df.j1 || fk >= df.Z) continue;
+            const Real* c = xs + (ly * (kUpTX + 2) + lx) * kUpRow + 4 + 4 * zq;
+            const P4<Real> xc = ldp<Real, 4>(c), xl = ldp<Real, 4>(c - kUpRow), xr = ldp<Real, 4>(c + kUpRow);
+            const P4<Real> yl = ldp<Real, 4>(c - (kUpTX + 2) * kUpRow), yr = ldp<Real, 4>(c + (kUpTX + 2) * kUpRow);
+            const Real zl = c[-1], zr = c[4];
+            const int g = fj * syf + fi * sxf + fk;
+            const P4<Real> rq = ldp<Real, 4>(r + g);
+            P4<Real> o;
+            Real dsum = Real(0);
+#pragma unroll
+            for (int m = 0; m < 4; ++m) {
+                const Real lo = (m == 0) ? zl : xc.a[m > 0 ? m - 1 : 0], hi = (m == 3) ? zr : xc.a[m < 3 ? m + 1 : 3];
+                const Real nb = (xl.a[m] + xr.a[m]) + (yl.a[m] + yr.a[m]) + (lo + hi);
+                const Real v = hd_fma(a1, nb, hd_fma(a0, xc.a[m], cj * rq.a[m]));
+                o.a[m] = v;
+                dsum = hd_fma(rq.a[m], v, dsum);
+            }
+            stp<Real, 4>(z + g, o);
+            if (FINAL && fj >= dj0 && fj < dj1) acc += (double)dsum;
+        }
+        __syncthreads();   // the next tile of this block reuses the shared arrays
+    }
+    if (FINAL) {
+        double tot;
+        if (block_sum_last(acc, S, 0, tot)) {
+            if (threadIdx.x == 0) { if (S->dist) S->loc[2] = tot; else { S->rz_old = S->rz; S->rz = tot; } }
+        }
+    }
+}
+
 // ---- fused down-pass for levels with Z % 4 == 0 --------------------------------------------------------------------
 // k_mg3_residual_rz_v4: res = r - (omega/6) M r for 4 z-consecutive cells per thread, restricted along z on the fly:
 //   resz[i, j, K] = 1/4 res[2K-1] + 3/4 res[2K] + 3/4 res[2K+1] + 1/4 res[2K+2]      (layout (Y, X, Z/2), z fastest)

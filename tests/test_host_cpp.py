@@ -132,3 +132,31 @@ def test_inksim_binary_end_to_end(tmp_path):
     assert np.array_equal(rec[:, 3:], np.stack([u.ravel(), v.ravel(), w.ravel()], axis=1))
     i, j, k = np.meshgrid(np.arange(8), np.arange(25), np.arange(8), indexing="ij")
     assert np.array_equal(rec[:, :3], np.stack([i.ravel(), j.ravel(), k.ravel()], axis=1).astype(np.float32) + 0.5)
+
+
+@pytest.mark.gpu
+def test_gpu_device_seeding_equals_the_reference_seeders():
+    """the emitter scene and the initParticles box produced by KERNELS (ink_seed_emitter / ink_seed_box; the host only
+    supplies the float loop counters with their sinf / cosf, or the rand() stream) equal the compiled reference's arrays bit for
+    bit — the emitter against the committed golden hashes, the box against the host seeder that the CPU tests pin."""
+    from ink_simulation_b200 import System, seeding
+
+    G = np.load(os.path.join(GOLD, "host_emitter.npz"))
+    dims = tuple(int(x) for x in G["dims"])
+    S = System(*dims)
+    assert seeding.seed_emitter_on_device(S) == int(G["n"]) == 324120
+    pos, vel = S.get_particles()
+    assert np.array_equal(pos[::997], G["pos_sample"]) and np.array_equal(vel[::997], G["vel_sample"])
+    assert hashlib.sha256(pos.tobytes()).hexdigest() == str(G["pos_sha"])
+    assert hashlib.sha256(vel.tobytes()).hexdigest() == str(G["vel_sha"])
+    S.close()
+    for dims, n in (((8, 25, 8), 10000), ((20, 45, 20), 100000), ((7, 9, 5), 333)):
+        S = System(*dims)
+        seeding.seed_box_on_device(S, n)
+        pos, vel = S.get_particles()
+        assert np.array_equal(pos, seeding.box_scene(dims, n)) and not vel.any()
+        # a second drop continues the same rand() stream, as initParticles does for NUM_PARTICLES = {n, m}
+        stream = seeding.rand_stream(3 * (n + 50))
+        seeding.seed_box_on_device(S, 50, drop=1, stream=stream[3 * n:])
+        assert np.array_equal(S.get_particles(1)[0], seeding.box_scene(dims, n + 50)[n:])
+        S.close()
