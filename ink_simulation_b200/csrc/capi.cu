@@ -379,6 +379,7 @@ struct Ctx final : CtxBase {
     // ncclAllGather.  Any failure (no peer access, odd row size, INK_NO_P2P=1) leaves p2p == false: the NCCL path is kept.
     int p2p_setup() {
         if (const char* e = getenv("INK_NO_P2P")) if (atoi(e) != 0) return 0;
+        if (const char* e = getenv("INK_NO_FOLD")) fold_ar = (atoi(e) == 0);
         if (world > kP2pMaxRanks) return 0;
         const size_t rowb = (size_t)g.sy * sizeof(Real);
         if (rowb % 16 != 0) return 0;
@@ -432,6 +433,15 @@ struct Ctx final : CtxBase {
         }
         if (int rc = allreduce(S->loc + off, (size_t)count, ncclDouble, ncclSum)) return rc;
         return cg_post(stage);
+    }
+    // the scalar all-reduce as the epilogue of the reducing kernel's last block (peer-memory path only; INK_NO_FOLD=1 = separate launch)
+    bool fold_ar = true;
+    ArFold make_fold(int off, int count, int stage) {
+        ArFold f{};
+        if (!(p2p && fold_ar)) return f;
+        f.on = 1; f.rank = rank; f.world = world; f.off = off; f.count = count; f.stage = stage; f.precond = use_mg ? 1 : 0;
+        f.peers = peers;
+        return f;
     }
     // boundary rows of the residual about to be produced (k_cg_init / k_cg_update) go straight into the neighbours' arenas
     P2pPush make_push() {
@@ -519,9 +529,12 @@ struct Ctx final : CtxBase {
         NK(nccl().GroupEnd());
         return 0;
     }
-    int allgather_velocity() {
+    int allgather_velocity() {   // the three components as ONE grouped NCCL operation (one launch, one pass of the protocol)
+        if (world == 1) return 0;
+        NK(nccl().GroupStart());
         for (int a = 0; a < 3; ++a)
-            if (int rc = allgather_rows(U(a), sizeof(Real))) return rc;
+            if (int rc = allgather_rows(U(a), sizeof(Real))) { nccl().GroupEnd(); return rc; }
+        NK(nccl().GroupEnd());
         return 0;
     }
     int allreduce(void* buf, size_t count, ncclDataType_t t, ncclRedOp_t op) {
@@ -1340,7 +1353,7 @@ struct Ctx final : CtxBase {
 
     // z = B r (result lv[0].xa, valid on own rows and `ovl` rows into each neighbour).  One GPU: one V-cycle.  Multi-GPU:
     // symmetric weighted overlapping Schwarz around the slab-local V-cycle — two band exchanges, no traffic inside the cycle.
-    int precondition(Real* r) {
+    int precondition(Real* r, const ArFold& fold = ArFold{}) {
         if (world == 1) { const int rc = mg_vcycle(r); TR("vcycle"); return rc; }
         const long long sy = g.sy;
         const size_t brow = (size_t)ovl * sy;
@@ -1356,34 +1369,36 @@ struct Ctx final : CtxBase {
         struct Band { int ja, jb, peer; };
         Band bands[2] = {{g.j0 - ovl, g.j0 + ovl, rank - 1}, {g.j1 - ovl, g.j1 + ovl, rank + 1}};
         const bool has[2] = {rank > 0, rank + 1 < world};
-        // band kernels: few blocks (each ends with a system-scope fence when it pushes to a peer), grid-stride
+        // band kernels: few blocks per side (each ends with a system-scope fence when it pushes to a peer), grid-stride; ONE launch
+        // per stage covers both sides of an interior rank (blocks [0, nb) side 0, [nb, 2 nb) side 1)
         const unsigned int bb = (unsigned int)std::min<long long>(2 * kSMs, (2 * (long long)brow + 255) / 256);
+        const unsigned long long z_seq = p2p ? ++p2p_seq[1] : 0ull;
+        BandArgs<Real> A{};
+        A.nb = (int)bb; A.r_seq = r_seq; A.z_seq = z_seq;
         for (int b = 0; b < 2; ++b)
             if (has[b]) {
-                if (p2p) LAUNCH_BAND(k_band_scale, bb, 256, S, sy, bands[b].ja, bands[b].jb, g.j0, g.j1, d_sw, r, band_save[b],
-                                (const Real*)(arena + off_halo[b]), b == 0 ? g.j0 - ovl : g.j1, (const unsigned long long*)&head_of(rank)->flag[0][b], r_seq);
-                else LAUNCH_BAND(k_band_scale, bb, 256, S, sy, bands[b].ja, bands[b].jb, g.j0, g.j1, d_sw, r, band_save[b], (const Real*)nullptr, 0,
-                            (const unsigned long long*)nullptr, 0ull);
+                BandSide<Real>& B = A.s[A.nsides++];
+                B.ja = bands[b].ja; B.jb = bands[b].jb; B.save = band_save[b];
+                if (p2p) {
+                    B.halo_src = reinterpret_cast<const Real*>(arena + off_halo[b]); B.halo_j0 = (b == 0) ? g.j0 - ovl : g.j1;
+                    B.wait_r = &head_of(rank)->flag[0][b];
+                    B.push_dst = reinterpret_cast<Real*>(peers.base[bands[b].peer] + off_band[1 - b]);
+                    B.push_flag = &head_of(bands[b].peer)->flag[1][1 - b];
+                    B.ticket = &head_of(rank)->ticket[2 + b];
+                    B.recv = reinterpret_cast<const Real*>(arena + off_band[b]);   // filled by the neighbour's k_band_restore_weight
+                    B.wait_z = &head_of(rank)->flag[1][b];
+                } else B.recv = band_recv[b];
             }
+        const unsigned int grid = bb * (unsigned int)A.nsides;
+        LAUNCH_BAND(k_band_scale, grid, 256, S, sy, A, g.j0, g.j1, d_sw, r);
         TR("band scale");
         if (int rc = mg_vcycle(r)) return rc;
         TR("vcycle");
         Real* z = lv[0].xa;
-        const unsigned long long z_seq = p2p ? ++p2p_seq[1] : 0ull;
-        for (int b = 0; b < 2; ++b)
-            if (has[b]) {
-                if (p2p) LAUNCH_BAND(k_band_restore_weight, bb, 256, S, sy, bands[b].ja, bands[b].jb, g.j0, g.j1, d_sw, r, band_save[b], z,
-                                (Real*)(peers.base[bands[b].peer] + off_band[1 - b]), &head_of(bands[b].peer)->flag[1][1 - b], z_seq, &head_of(rank)->ticket[2 + b]);
-                else LAUNCH_BAND(k_band_restore_weight, bb, 256, S, sy, bands[b].ja, bands[b].jb, g.j0, g.j1, d_sw, r, band_save[b], z, (Real*)nullptr,
-                            (unsigned long long*)nullptr, 0ull, (unsigned int*)nullptr);
-            }
+        LAUNCH_BAND(k_band_restore_weight, grid, 256, S, sy, A, g.j0, g.j1, d_sw, r, z);
         CK(cudaGetLastError());
         TR("band weight");
-        const Real* recv[2] = {band_recv[0], band_recv[1]};
-        if (p2p) {   // the weighted bands are already in the neighbours' arenas (k_band_restore_weight pushed them); combine waits for ours
-            recv[0] = reinterpret_cast<const Real*>(arena + off_band[0]);
-            recv[1] = reinterpret_cast<const Real*>(arena + off_band[1]);
-        } else {
+        if (!p2p) {
             NK(nccl().GroupStart());
             for (int b = 0; b < 2; ++b)
                 if (has[b]) {
@@ -1392,9 +1407,7 @@ struct Ctx final : CtxBase {
                 }
             NK(nccl().GroupEnd());
         }
-        for (int b = 0; b < 2; ++b)
-            if (has[b]) LAUNCH_BAND(k_band_combine, bb, 256, S, sy, bands[b].ja, bands[b].jb, g.j0, g.j1, recv[b], r, z,
-                               p2p ? (const unsigned long long*)&head_of(rank)->flag[1][b] : (const unsigned long long*)nullptr, z_seq);
+        LAUNCH_BAND(k_band_combine, grid, 256, S, sy, A, g.j0, g.j1, (const Real*)r, z, fold);   // + the folded all-reduce of <r,r>, <r,z>
 #undef LAUNCH_BAND
         TR("z band combine");
         CK(cudaGetLastError());
@@ -1442,12 +1455,13 @@ struct Ctx final : CtxBase {
         const int hlo = (dist && rank > 0) ? 1 : 0, hhi = (dist && rank + 1 < world) ? 1 : 0;
         if (int rc = halo_exchange(x, 1, 1)) return rc;     // warm start: the initial residual needs x on the neighbour rows
         { const P2pPush push = make_push();
-          if (vec4()) LAUNCH((k_cg_init<Real, 4>), nb, 256, g, S, f, x, cg_r, push);
-          else LAUNCH((k_cg_init<Real, 1>), nb, 256, g, S, f, x, cg_r, push); }
-        CK(cudaGetLastError());
-        if (dist) {
-            if (int rc = ar_post(0, 4, 0)) return rc;
-        }
+          const ArFold fold = make_fold(0, 4, 0);
+          if (vec4()) LAUNCH((k_cg_init<Real, 4>), nb, 256, g, S, f, x, cg_r, push, fold);
+          else LAUNCH((k_cg_init<Real, 1>), nb, 256, g, S, f, x, cg_r, push, fold);
+          CK(cudaGetLastError());
+          if (dist && !fold.on) {
+              if (int rc = ar_post(0, 4, 0)) return rc;
+          } }
         const size_t head = offsetof(CgScal, partial);
         // Steady state (one GPU, preconditioned, the last solve took > 1 iteration): do NOT wait for the initial residual —
         // the first batch below is launched blind anyway.  (Measured on B200 at 128x256x128: 1.95 vs 1.97 ms per step, i.e.
@@ -1469,9 +1483,10 @@ struct Ctx final : CtxBase {
         int dcur = 0, launched = 0;
         Real* zsrc = cg_r;
         if (use_mg) {
-            if (int rc = precondition(cg_r)) return rc;
+            const ArFold fold = make_fold(2, 1, 3);
+            if (int rc = precondition(cg_r, fold)) return rc;
             zsrc = lv[0].xa;
-            if (dist) {
+            if (dist && !fold.on) {
                 if (int rc = ar_post(2, 1, 3)) return rc;
             }
         } else if (int rc = halo_exchange(zsrc, 1, 1)) return rc;
@@ -1481,10 +1496,11 @@ struct Ctx final : CtxBase {
         // one PCG iteration: direction + matvec, update, preconditioner (+ the distributed reductions / exchanges)
         auto iteration_body = [&](int dc) -> int {
             TR("start");
-            if (vec4()) LAUNCH((k_cg_dir_matvec<Real, 4>), nb, 256, g, S, zsrc, cg_d[dc], cg_d[dc ^ 1], cg_w, hlo, hhi);
-            else LAUNCH((k_cg_dir_matvec<Real, 1>), nb, 256, g, S, zsrc, cg_d[dc], cg_d[dc ^ 1], cg_w, hlo, hhi);
+            const ArFold fold1 = make_fold(0, 1, 1);
+            if (vec4()) LAUNCH((k_cg_dir_matvec<Real, 4>), nb, 256, g, S, zsrc, cg_d[dc], cg_d[dc ^ 1], cg_w, hlo, hhi, fold1);
+            else LAUNCH((k_cg_dir_matvec<Real, 1>), nb, 256, g, S, zsrc, cg_d[dc], cg_d[dc ^ 1], cg_w, hlo, hhi, fold1);
             TR("matvec");
-            if (dist) {
+            if (dist && !fold1.on) {
                 if (int rc = ar_post(0, 1, 1)) return rc;
             }
             TR("allreduce dw");
@@ -1497,10 +1513,12 @@ struct Ctx final : CtxBase {
                 else LAUNCH((k_cg_update<Real, 1, false>), nb, 256, g, S, x, cg_r, cg_d[dc ^ 1], cg_w, push);
             }
             TR("update");
+            const ArFold fold2 = use_mg ? make_fold(1, 2, 2) : ArFold{};
             if (use_mg)
-                if (int rc = precondition(cg_r)) return rc;
+                if (int rc = precondition(cg_r, fold2)) return rc;
             if (dist) {
-                if (int rc = ar_post(1, 2, 2)) return rc;
+                if (!fold2.on)
+                    if (int rc = ar_post(1, 2, 2)) return rc;
                 TR("allreduce rr,rz");
                 if (!use_mg)
                     if (int rc = halo_exchange(zsrc, 1, 1)) return rc;

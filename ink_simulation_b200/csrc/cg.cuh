@@ -17,7 +17,7 @@
 namespace ink {
 
 constexpr int kCgBlocks = 148 * 8;       // grid of the CG kernels (grid-stride)
-constexpr int kCgMaxBlocks = 148 * 32;   // capacity of the per-block fp64 partials (largest grid any reducing kernel may use)
+constexpr int kCgMaxBlocks = 148 * 64;   // capacity of the per-block fp64 partials (largest grid any reducing kernel may use)
 
 struct CgScal {
     double rr, rr_old, dw, bb, tol2;
@@ -28,6 +28,103 @@ struct CgScal {
     double loc[4];       // [0] <d,w>  [1] <r,r>  [2] <r,z>  [3] <f,f>
     double partial[2][kCgMaxBlocks];
 };
+
+constexpr int kP2pMaxRanks = 16;
+
+struct alignas(64) P2pMail {
+    double v[4];
+    unsigned long long seq;
+    unsigned long long pad[3];
+};
+
+// the head of every rank's arena (payload regions follow at byte offsets the host computes, identical on all ranks)
+struct P2pHead {
+    P2pMail mail[2][kP2pMaxRanks];          // [slot][source rank]
+    unsigned long long flag[4][2];          // [channel][side 0 = from rank-1, 1 = from rank+1] last sequence delivered
+    unsigned long long mail_seq;            // LOCAL: all-reduces this rank has taken part in (kept on the device so that
+                                            // calls skipped after convergence do not advance it)
+    unsigned int ticket[4];                 // LOCAL: block tickets of the pushing band kernels ([2 + side])
+};
+
+struct P2pPeers {
+    unsigned char* base[kP2pMaxRanks];      // arena of every rank as mapped in THIS process (own arena at [rank])
+};
+
+// Scalar all-reduce folded into the kernel that produces the partial sums: the LAST block of a reducing kernel (cg_init,
+// cg_dir_matvec, the last band_combine of an iteration) runs the mailbox exchange itself instead of a separate one-warp launch
+// (two launches fewer on the critical path of every distributed PCG iteration).
+struct ArFold {
+    int on, rank, world, off, count, stage, precond;
+    P2pPeers peers;
+};
+
+// ---- scalar all-reduce (sum of `count` <= 4 doubles starting at S->loc[off]) fused with the CG scalar epilogue ---------
+// One warp: lane p < world stores this rank's partials into rank p's mailbox, then waits for rank p's partials in the
+// local mailbox; lane 0 adds them in rank order (identical result on every rank) and applies k_cg_post's logic.
+__device__ __forceinline__ void cg_post_apply(CgScal* S, int stage, int precond) {
+    if (stage == 0) {
+        S->rr = S->loc[1]; S->rr_old = S->loc[1]; S->bb = S->loc[3]; S->dw = 0;
+        S->rz = S->loc[1]; S->rz_old = S->loc[1];
+        S->iters = 0;
+        S->done = (S->loc[1] <= S->tol2 * S->loc[3]) ? 1 : 0;
+    } else if (stage == 1) {
+        S->dw = S->loc[0];
+    } else if (stage == 2) {
+        S->rr_old = S->rr; S->rr = S->loc[1];
+        S->rz_old = S->rz; S->rz = precond ? S->loc[2] : S->loc[1];
+        S->iters += 1;
+        if (S->loc[1] <= S->tol2 * S->bb) S->done = 1;
+    } else {
+        S->rz_old = S->loc[2]; S->rz = S->loc[2];
+    }
+}
+
+// executed by ONE FULL WARP (all 32 lanes converged)
+__device__ __forceinline__ void p2p_allreduce_post_warp(CgScal* S, const P2pPeers& peers, int rank, int world, int off, int count, int stage, int precond) {
+    const int lane = threadIdx.x & 31;
+    P2pHead* me = reinterpret_cast<P2pHead*>(peers.base[rank]);
+    const unsigned long long seq = me->mail_seq + 1;
+    const int slot = (int)(seq & 1ull);
+    if (lane < world) {
+        P2pMail* dst = &reinterpret_cast<P2pHead*>(peers.base[lane])->mail[slot][rank];
+        for (int a = 0; a < count; ++a) dst->v[a] = S->loc[off + a];
+        __threadfence_system();
+        *reinterpret_cast<volatile unsigned long long*>(&dst->seq) = seq;
+    }
+    double got[4] = {0, 0, 0, 0};
+    if (lane < world) {
+        const P2pMail* src = &me->mail[slot][lane];
+        volatile const unsigned long long* f = reinterpret_cast<const volatile unsigned long long*>(&src->seq);
+        while (*f < seq) {
+#if defined(__CUDA_ARCH__) && __CUDA_ARCH__ >= 700
+            __nanosleep(32);
+#endif
+        }
+        __threadfence_system();
+        for (int a = 0; a < count; ++a) got[a] = *reinterpret_cast<const volatile double*>(&src->v[a]);
+    }
+    __syncwarp();
+    for (int a = 0; a < count; ++a) {       // fixed rank order 0, 1, .. world-1 on every rank
+        double tot = 0;
+        for (int p = 0; p < world; ++p) tot += __shfl_sync(0xffffffffu, got[a], p);
+        if (lane == 0) S->loc[off + a] = tot;
+    }
+    __syncwarp();
+    if (lane == 0) {
+        me->mail_seq = seq;
+        cg_post_apply(S, stage, precond);
+    }
+}
+__device__ __forceinline__ void p2p_fold(CgScal* S, const ArFold& f) {   // warp 0 of the last block, after thread 0 stored S->loc
+    __syncwarp();
+    p2p_allreduce_post_warp(S, f.peers, f.rank, f.world, f.off, f.count, f.stage, f.precond);
+}
+
+__global__ void __launch_bounds__(32) k_p2p_allreduce_post(CgScal* S, P2pPeers peers, int rank, int world, int off, int count, int stage, int precond) {
+    INK_PDL();
+    if (stage != 0 && S->done) return;      // every rank holds the same `done` (same sums): all skip together
+    p2p_allreduce_post_warp(S, peers, rank, world, off, count, stage, precond);
+}
 
 template <class Real, int V>
 struct alignas(sizeof(Real) * V) Pack { Real a[V]; };
@@ -73,12 +170,19 @@ __device__ __forceinline__ bool block_sum_last(double acc, CgScal* S, int slot, 
     __syncthreads();
     if (!is_last) return false;
     __threadfence();
-    if (wid == 0) {
-        double s = 0;
-        for (int q = lane; q < (int)gridDim.x; q += 32) s += __ldcg(&S->partial[slot][q]);
-        s = warp_sum(s);
-        total = s;
-        if (lane == 0) S->ticket = 0;
+    // final pass by the WHOLE last block, fixed order for a given grid size (deterministic): thread t adds partials t, t + B, ...;
+    // warp shuffle; warp totals in warp order.  (One warp walking up to 9472 partials alone took microseconds.)
+    double s = 0;
+    for (int q = threadIdx.x; q < (int)gridDim.x; q += blockDim.x) s += __ldcg(&S->partial[slot][q]);
+    s = warp_sum(s);
+    __syncthreads();              // ssum is reused
+    if (lane == 0) ssum[wid] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double b = 0;
+        for (int q = 0; q < (int)(blockDim.x >> 5); ++q) b += ssum[q];
+        total = b;
+        S->ticket = 0;
     }
     return true;
 }
@@ -95,7 +199,8 @@ __device__ __forceinline__ void vec_cell(const Grid& g, long long t, int ZV, int
 
 // r = f - M x, <r,r>, <f,f>;  (x may be a warm start)
 template <class Real, int V>
-__global__ void __launch_bounds__(256) k_cg_init(Grid g, CgScal* S, const Real* __restrict__ f, const Real* __restrict__ x, Real* __restrict__ r, P2pPush push) {
+__global__ void __launch_bounds__(256) k_cg_init(Grid g, CgScal* S, const Real* __restrict__ f, const Real* __restrict__ x, Real* __restrict__ r, P2pPush push,
+                                                 ArFold fold) {
     INK_PDL();
     const int ZV = g.Z / V;
     const long long nvec = (long long)(g.j1 - g.j0) * g.X * ZV;
@@ -169,13 +274,14 @@ __global__ void __launch_bounds__(256) k_cg_init(Grid g, CgScal* S, const Real* 
                     S->done = (tot_rr <= S->tol2 * tot_bb) ? 1 : 0;
                 }
             }
+            if (fold.on) p2p_fold(S, fold);
         }
     }
 }
 
 template <class Real, int V>
 __global__ void __launch_bounds__(256) k_cg_dir_matvec(Grid g, CgScal* S, const Real* __restrict__ r, const Real* __restrict__ d,
-                                                       Real* __restrict__ dn, Real* __restrict__ w, int halo_lo, int halo_hi) {
+                                                       Real* __restrict__ dn, Real* __restrict__ w, int halo_lo, int halo_hi, ArFold fold) {
     INK_PDL();
     if (S->done) return;
     const Real beta = (S->iters == 0) ? Real(0) : (Real)(S->rz / S->rz_old);
@@ -233,6 +339,7 @@ __global__ void __launch_bounds__(256) k_cg_dir_matvec(Grid g, CgScal* S, const 
     double tot;
     if (block_sum_last(acc, S, 0, tot)) {
         if (threadIdx.x == 0) { if (S->dist) S->loc[0] = tot; else S->dw = tot; }
+        if (fold.on && threadIdx.x < 32) p2p_fold(S, fold);
     }
 }
 

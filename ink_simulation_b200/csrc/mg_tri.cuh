@@ -390,7 +390,8 @@ __global__ void __launch_bounds__(256, 3) k_mg3_up(CgScal* S, MgDims df, MgDims 
 //   B      z = c r + (1-omega) x' + (omega/6) N x' from shared memory (5 LDS.128 + 2 LDS.32 per quad), one STG.128, <r,z>.
 // ~38 instructions per fine cell instead of ~85.  Same operator as mg3_up (cells outside the grid / slab hold x' = 0, which is
 // "N sums existing neighbours only"); different rounding order.  Z % 4 == 0 (vector accesses); any X, Y, slab start.
-constexpr int kUpTX = 8, kUpTY = 8, kUpTZ = 64;
+constexpr int kUpTX = 8, kUpTY = 8, kUpTZ = 64;   // measured: 8x8x32 tiles (8 blocks per SM, no wave tail) are SLOWER — 32.8 / 104.6 us against 26.7 / 75.8 us
+                                                 // at 128x256x128 / 256^3 (profiles/r2_f_*): the halo and the staging per tile cost more than the tail
 constexpr int kUpRows = (kUpTX + 2) * (kUpTY + 2);       // fine rows of the tile + halo
 constexpr int kUpRow = kUpTZ + 8;                        // [3 pad][k = -1][TZ cells][k = TZ][3 pad]: cell k at 4 + k, 16-byte aligned quads
 constexpr int kUpCX = kUpTX / 2 + 2, kUpCY = kUpTY / 2 + 2, kUpCZ = kUpTZ / 2 + 2;
@@ -423,10 +424,14 @@ __global__ void __launch_bounds__(256) k_mg3_up_tile(CgScal* S, MgDims df, MgDim
         const int fx0 = tx_ * kUpTX, fy0 = jbase + ty_ * kUpTY, fz0 = tz_ * kUpTZ;
         const int cx0 = (fx0 >> 1) - 1, cy0 = (fy0 >> 1) - 1, cz0 = (fz0 >> 1) - 1;
         // ---- stage the coarse values (zero outside the coarse grid / slab: dropped donors)
-        for (int q = tid; q < kUpCX * kUpCY * kUpCZ; q += 256) {
-            const int kk = q % kUpCZ, col = q / kUpCZ, ci = cx0 + col % kUpCX, cjj = cy0 + col / kUpCX, ck = cz0 + kk;
-            const bool ok = ci >= 0 && ci < dc.X && cjj >= dc.j0 && cjj < dc.j1 && ck >= 0 && ck < dc.Z;
-            es[col * kUpCRow + kk] = ok ? e[((long long)cjj * dc.X + ci) * dc.Z + ck] : Real(0);
+        for (int col = tid >> 5; col < kUpCX * kUpCY; col += 8) {   // one warp per coarse column: validity and base address once per column
+            const int ci = cx0 + col % kUpCX, cjj = cy0 + col / kUpCX;
+            const bool okc = ci >= 0 && ci < dc.X && cjj >= dc.j0 && cjj < dc.j1;
+            const Real* src = e + ((long long)cjj * dc.X + ci) * dc.Z + cz0;
+            for (int kk = tid & 31; kk < kUpCZ; kk += 32) {
+                const int ck = cz0 + kk;
+                es[col * kUpCRow + kk] = (okc && ck >= 0 && ck < dc.Z) ? src[kk] : Real(0);
+            }
         }
         __syncthreads();
         // ---- A: x' on the tile + halo rows, one z-quad per thread and pass

@@ -184,27 +184,47 @@ __global__ void __launch_bounds__(256) k_mg_residual_restrict_v4(const CgScal* S
 // exchanges per iteration instead of ~5 per level.  All three kernels run over one band of rows [ja, jb).
 // VEC = elements per access (16 bytes when a row is a multiple of 16 bytes — always on the peer-memory path — else 1).
 // t runs over the band in units of VEC elements; a band is < 2^31 cells.
+// One launch covers BOTH bands of an interior rank (two neighbours): blocks [0, nb) work on side 0, [nb, 2 nb) on side 1 — three
+// launches and three serialised peer waits fewer per PCG iteration than one launch per side.
+template <class Real>
+struct BandSide {
+    int ja, jb;                              // band rows [ja, jb)
+    Real* save;                              // unscaled own rows of the band (restored after the cycle)
+    const Real* halo_src; int halo_j0;       // peer-memory path: where the neighbour pushed its r rows (nullptr: they are in r already)
+    const unsigned long long* wait_r;        // flag the neighbour publishes after pushing r   (k_band_scale)
+    Real* push_dst; unsigned long long* push_flag; unsigned int* ticket;   // weighted z band -> neighbour's arena (k_band_restore_weight)
+    const Real* recv; const unsigned long long* wait_z;                    // neighbour's weighted band (k_band_combine)
+};
+template <class Real>
+struct BandArgs {
+    int nsides, nb;                          // blocks per side
+    BandSide<Real> s[2];
+    unsigned long long r_seq, z_seq;
+};
+
 template <class Real, int VEC>
-__global__ void __launch_bounds__(256) k_band_scale(const CgScal* S, long long sy, int ja, int jb, int own0, int own1, const Real* __restrict__ sw,
-                                                    Real* __restrict__ r, Real* __restrict__ save, const Real* halo_src, int halo_j0,
-                                                    const unsigned long long* wait_flag, unsigned long long seq) {
+__global__ void __launch_bounds__(256) k_band_scale(const CgScal* S, long long sy, BandArgs<Real> A, int own0, int own1, const Real* __restrict__ sw,
+                                                    Real* __restrict__ r) {
     INK_PDL();
     if (S->done) return;
+    const int side = (int)blockIdx.x >= A.nb ? 1 : 0;
+    const BandSide<Real>& B = A.s[side];
+    const unsigned int bid = blockIdx.x - side * A.nb;
     // peer-memory path: the neighbour's rows were pushed into this rank's arena by the kernel that produced them (P2pPush);
     // wait for its sequence number, then take them from there (L2) instead of from r
-    if (wait_flag) {
-        if (threadIdx.x == 0) p2p_spin(reinterpret_cast<const volatile unsigned long long*>(wait_flag), seq);
+    if (B.wait_r) {
+        if (threadIdx.x == 0) p2p_spin(reinterpret_cast<const volatile unsigned long long*>(B.wait_r), A.r_seq);
         __syncthreads();
     }
-    const unsigned int syv = (unsigned int)(sy / VEC), n = (unsigned int)(jb - ja) * syv;
-    for (unsigned int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
+    const unsigned int syv = (unsigned int)(sy / VEC), n = (unsigned int)(B.jb - B.ja) * syv;
+    for (unsigned int t = bid * blockDim.x + threadIdx.x; t < n; t += A.nb * blockDim.x) {
         const unsigned int jr = t / syv;
-        const int j = ja + (int)jr;
-        const long long e = (long long)t * VEC, c = (long long)ja * sy + e;
+        const int j = B.ja + (int)jr;
+        const long long e = (long long)t * VEC, c = (long long)B.ja * sy + e;
         Pack<Real, VEC> v;
-        if (j >= own0 && j < own1) { v = ldp<Real, VEC>(r + c); stp<Real, VEC>(save + e, v); }   // own rows are restored after the cycle
-        else if (halo_src) {
-            const Real* hp = halo_src + ((long long)(j - halo_j0) * sy + (e - (long long)jr * sy));
+        if (j >= own0 && j < own1) { v = ldp<Real, VEC>(r + c); stp<Real, VEC>(B.save + e, v); }   // own rows are restored after the cycle
+        else if (B.halo_src) {
+            const Real* hp = B.halo_src + ((long long)(j - B.halo_j0) * sy + (e - (long long)jr * sy));
 #pragma unroll
             for (int a = 0; a < VEC; ++a) v.a[a] = __ldcg(hp + a);
         } else v = ldp<Real, VEC>(r + c);
@@ -215,58 +235,63 @@ __global__ void __launch_bounds__(256) k_band_scale(const CgScal* S, long long s
     }
 }
 template <class Real, int VEC>
-__global__ void __launch_bounds__(256) k_band_restore_weight(const CgScal* S, long long sy, int ja, int jb, int own0, int own1, const Real* __restrict__ sw,
-                                                             Real* __restrict__ r, const Real* __restrict__ save, Real* __restrict__ z, Real* push_dst,
-                                                             unsigned long long* push_flag, unsigned long long seq, unsigned int* ticket) {
+__global__ void __launch_bounds__(256) k_band_restore_weight(const CgScal* S, long long sy, BandArgs<Real> A, int own0, int own1, const Real* __restrict__ sw,
+                                                             Real* __restrict__ r, Real* __restrict__ z) {
     INK_PDL();
     if (S->done) return;
-    const unsigned int syv = (unsigned int)(sy / VEC), n = (unsigned int)(jb - ja) * syv;
-    for (unsigned int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
-        const int j = ja + (int)(t / syv);
-        const long long e = (long long)t * VEC, c = (long long)ja * sy + e;
-        if (j >= own0 && j < own1) stp<Real, VEC>(r + c, ldp<Real, VEC>(save + e));
+    const int side = (int)blockIdx.x >= A.nb ? 1 : 0;
+    const BandSide<Real>& B = A.s[side];
+    const unsigned int bid = blockIdx.x - side * A.nb;
+    const unsigned int syv = (unsigned int)(sy / VEC), n = (unsigned int)(B.jb - B.ja) * syv;
+    for (unsigned int t = bid * blockDim.x + threadIdx.x; t < n; t += A.nb * blockDim.x) {
+        const int j = B.ja + (int)(t / syv);
+        const long long e = (long long)t * VEC, c = (long long)B.ja * sy + e;
+        if (j >= own0 && j < own1) stp<Real, VEC>(r + c, ldp<Real, VEC>(B.save + e));
         Pack<Real, VEC> zz = ldp<Real, VEC>(z + c);
         const Real w = sw[j];
 #pragma unroll
         for (int a = 0; a < VEC; ++a) zz.a[a] *= w;
         stp<Real, VEC>(z + c, zz);
-        if (push_dst) stp<Real, VEC>(push_dst + e, zz);   // peer-memory path: the weighted band goes straight into the neighbour's arena
+        if (B.push_dst) stp<Real, VEC>(B.push_dst + e, zz);   // peer-memory path: the weighted band goes straight into the neighbour's arena
     }
-    if (push_dst) {   // last block to finish publishes the sequence number (every block fenced its remote stores first)
+    if (B.push_dst) {   // the side's last block to finish publishes the sequence number (every block fenced its remote stores first)
         __threadfence_system();
         __syncthreads();
         if (threadIdx.x == 0) {
-            if (atomicAdd(ticket, 1u) == gridDim.x - 1) {
-                *ticket = 0;
+            if (atomicAdd(B.ticket, 1u) == (unsigned int)A.nb - 1) {
+                *B.ticket = 0;
                 __threadfence_system();
-                *reinterpret_cast<volatile unsigned long long*>(push_flag) = seq;
+                *reinterpret_cast<volatile unsigned long long*>(B.push_flag) = A.z_seq;
             }
         }
     }
 }
-// z += the neighbour's contribution on the band; adds <r, z> over this rank's own band rows to S->loc[2]
+// z += the neighbour's contribution on the band(s); adds <r, z> over this rank's own band rows to S->loc[2]; the last block of the
+// launch — the iteration's last reducing kernel — also carries the folded all-reduce of <r,r>, <r,z> (ArFold)
 template <class Real, int VEC>
-__global__ void __launch_bounds__(256) k_band_combine(CgScal* S, long long sy, int ja, int jb, int own0, int own1, const Real* recv,
-                                                      const Real* __restrict__ r, Real* __restrict__ z, const unsigned long long* wait_flag,
-                                                      unsigned long long seq) {
+__global__ void __launch_bounds__(256) k_band_combine(CgScal* S, long long sy, BandArgs<Real> A, int own0, int own1, const Real* __restrict__ r,
+                                                      Real* __restrict__ z, ArFold fold) {
     INK_PDL();
     if (S->done) return;
-    if (wait_flag) {   // peer-memory path: recv is this rank's arena, filled by the neighbour's k_band_restore_weight
-        if (threadIdx.x == 0) p2p_spin(reinterpret_cast<const volatile unsigned long long*>(wait_flag), seq);
+    const int side = (int)blockIdx.x >= A.nb ? 1 : 0;
+    const BandSide<Real>& B = A.s[side];
+    const unsigned int bid = blockIdx.x - side * A.nb;
+    if (B.wait_z) {   // peer-memory path: recv is this rank's arena, filled by the neighbour's k_band_restore_weight
+        if (threadIdx.x == 0) p2p_spin(reinterpret_cast<const volatile unsigned long long*>(B.wait_z), A.z_seq);
         __syncthreads();
     }
-    const unsigned int syv = (unsigned int)(sy / VEC), n = (unsigned int)(jb - ja) * syv;
+    const unsigned int syv = (unsigned int)(sy / VEC), n = (unsigned int)(B.jb - B.ja) * syv;
     double acc = 0;
-    for (unsigned int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
-        const int j = ja + (int)(t / syv);
-        const long long e = (long long)t * VEC, c = (long long)ja * sy + e;
+    for (unsigned int t = bid * blockDim.x + threadIdx.x; t < n; t += A.nb * blockDim.x) {
+        const int j = B.ja + (int)(t / syv);
+        const long long e = (long long)t * VEC, c = (long long)B.ja * sy + e;
         Pack<Real, VEC> v = ldp<Real, VEC>(z + c);
         const bool own = (j >= own0 && j < own1);
         Pack<Real, VEC> rc;
         if (own) rc = ldp<Real, VEC>(r + c);
 #pragma unroll
         for (int a = 0; a < VEC; ++a) {
-            v.a[a] += __ldcg(recv + e + a);
+            v.a[a] += __ldcg(B.recv + e + a);
             if (own) acc += (double)rc.a[a] * (double)v.a[a];
         }
         stp<Real, VEC>(z + c, v);
@@ -274,6 +299,7 @@ __global__ void __launch_bounds__(256) k_band_combine(CgScal* S, long long sy, i
     double tot;
     if (block_sum_last(acc, S, 1, tot)) {
         if (threadIdx.x == 0) S->loc[2] += tot;
+        if (fold.on && threadIdx.x < 32) p2p_fold(S, fold);
     }
 }
 

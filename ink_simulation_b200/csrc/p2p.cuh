@@ -17,78 +17,7 @@
 
 namespace ink {
 
-constexpr int kP2pMaxRanks = 16;
-
-struct alignas(64) P2pMail {
-    double v[4];
-    unsigned long long seq;
-    unsigned long long pad[3];
-};
-
-// the head of every rank's arena (payload regions follow at byte offsets the host computes, identical on all ranks)
-struct P2pHead {
-    P2pMail mail[2][kP2pMaxRanks];          // [slot][source rank]
-    unsigned long long flag[4][2];          // [channel][side 0 = from rank-1, 1 = from rank+1] last sequence delivered
-    unsigned long long mail_seq;            // LOCAL: all-reduces this rank has taken part in (kept on the device so that
-                                            // calls skipped after convergence do not advance it)
-    unsigned int ticket[4];                 // LOCAL: block tickets of the pushing band kernels ([2 + side])
-};
-
-struct P2pPeers {
-    unsigned char* base[kP2pMaxRanks];      // arena of every rank as mapped in THIS process (own arena at [rank])
-};
-
-// ---- scalar all-reduce (sum of `count` <= 4 doubles starting at S->loc[off]) fused with the CG scalar epilogue ---------
-// One warp: lane p < world stores this rank's partials into rank p's mailbox, then waits for rank p's partials in the
-// local mailbox; lane 0 adds them in rank order (identical result on every rank) and applies k_cg_post's logic.
-__device__ __forceinline__ void cg_post_apply(CgScal* S, int stage, int precond) {
-    if (stage == 0) {
-        S->rr = S->loc[1]; S->rr_old = S->loc[1]; S->bb = S->loc[3]; S->dw = 0;
-        S->rz = S->loc[1]; S->rz_old = S->loc[1];
-        S->iters = 0;
-        S->done = (S->loc[1] <= S->tol2 * S->loc[3]) ? 1 : 0;
-    } else if (stage == 1) {
-        S->dw = S->loc[0];
-    } else if (stage == 2) {
-        S->rr_old = S->rr; S->rr = S->loc[1];
-        S->rz_old = S->rz; S->rz = precond ? S->loc[2] : S->loc[1];
-        S->iters += 1;
-        if (S->loc[1] <= S->tol2 * S->bb) S->done = 1;
-    } else {
-        S->rz_old = S->loc[2]; S->rz = S->loc[2];
-    }
-}
-
-__global__ void __launch_bounds__(32) k_p2p_allreduce_post(CgScal* S, P2pPeers peers, int rank, int world, int off, int count, int stage, int precond) {
-    INK_PDL();
-    if (stage != 0 && S->done) return;      // every rank holds the same `done` (same sums): all skip together
-    const int lane = threadIdx.x;
-    P2pHead* me = reinterpret_cast<P2pHead*>(peers.base[rank]);
-    const unsigned long long seq = me->mail_seq + 1;
-    const int slot = (int)(seq & 1ull);
-    if (lane < world) {
-        P2pMail* dst = &reinterpret_cast<P2pHead*>(peers.base[lane])->mail[slot][rank];
-        for (int a = 0; a < count; ++a) dst->v[a] = S->loc[off + a];
-        __threadfence_system();
-        *reinterpret_cast<volatile unsigned long long*>(&dst->seq) = seq;
-    }
-    double got[4] = {0, 0, 0, 0};
-    if (lane < world) {
-        const P2pMail* src = &me->mail[slot][lane];
-        p2p_spin(reinterpret_cast<const volatile unsigned long long*>(&src->seq), seq);
-        for (int a = 0; a < count; ++a) got[a] = *reinterpret_cast<const volatile double*>(&src->v[a]);
-    }
-    for (int a = 0; a < count; ++a) {       // fixed rank order 0, 1, .. world-1 on every rank
-        double tot = 0;
-        for (int p = 0; p < world; ++p) tot += __shfl_sync(0xffffffffu, got[a], p);
-        if (lane == 0) S->loc[off + a] = tot;
-    }
-    __syncwarp();
-    if (lane == 0) {
-        me->mail_seq = seq;
-        cg_post_apply(S, stage, precond);
-    }
-}
+// (P2pMail / P2pHead / P2pPeers, the scalar all-reduce and its fold-in form live in cg.cuh, next to the kernels that end with them)
 
 // ---- boundary bands ------------------------------------------------------------------------------------------------------
 // There are no stand-alone put / wait kernels: the PRODUCER of a band stores it a second time into the neighbour's arena
