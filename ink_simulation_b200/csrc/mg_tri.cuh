@@ -388,6 +388,8 @@ __global__ void __launch_bounds__(256, 3) k_mg3_up(CgScal* S, MgDims df, MgDims 
 //   A      x' = c r + P e for the tile plus a one-cell halo, four z-consecutive cells per thread (separable: 28 FMAs per
 //          quad from 16 shared coarse values, one LDG.128 of r), into shared memory — each x' once (1.6x with the halo),
 //   B      z = c r + (1-omega) x' + (omega/6) N x' from shared memory (5 LDS.128 + 2 LDS.32 per quad), one STG.128, <r,z>.
+// (Measured and rejected, profiles/r2_f_*: a thread layout that does the row arithmetic once per two quads — 8 z-lanes x 32 row-lanes —
+// is slower, 30.6 / 90 us against 26.7 / 75.8 us: four rows per warp instruction instead of two.)
 // ~38 instructions per fine cell instead of ~85.  Same operator as mg3_up (cells outside the grid / slab hold x' = 0, which is
 // "N sums existing neighbours only"); different rounding order.  Z % 4 == 0 (vector accesses); any X, Y, slab start.
 constexpr int kUpTX = 8, kUpTY = 8, kUpTZ = 64;   // measured: 8x8x32 tiles (8 blocks per SM, no wave tail) are SLOWER — 32.8 / 104.6 us against 26.7 / 75.8 us
