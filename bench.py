@@ -616,8 +616,8 @@ def main():
         e2e = {"value": n / (ms_e2e * 1e-3), "unit": "particle-updates/s", "ms_per_step": ms_e2e,
                "h2d_bytes_per_step": n_local * 12, "d2h_bytes_per_step": n_local * 12,
                "mode": "blocking calls" if args.e2e_blocking else "streaming calls: H2D(i+1) and D2H(i-1) overlap step i", "steps": k2}
-        if world > 1:
-            # copy-only loop (no ink_step): what the host side of the box can move with N ranks copying at once
+        if True:
+            # copy-only loop (no ink_step): the PCIe / host-memory floor of this e2e pattern with N ranks copying at once
             S.sync_io()
             H.barrier()
             e0.record(ext)
@@ -633,8 +633,8 @@ def main():
             ms_copy = H.max_over_ranks(e0.elapsed_time(e1)) / k2
             e2e["copy_only_ms_per_step"] = ms_copy
             e2e["copy_only_aggregate_gbs"] = 24 * n / ms_copy / 1e6
-            e2e["note"] = ("copy_only = the same H2D + D2H traffic with no compute in between: the host-memory / PCIe ceiling of the box with "
-                           f"{world} ranks copying at once")
+            e2e["note"] = ("copy_only = the same H2D + D2H traffic with no compute in between: the host-memory / PCIe floor of the box with "
+                           f"{world} rank(s) copying at once; e2e cannot be faster than that")
 
     # ---- per-kernel micro-timings (CUDA events on the library stream, same process, after the timed region) -------------
     peak, peak_src = peaks()

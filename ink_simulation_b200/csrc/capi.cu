@@ -159,6 +159,7 @@ struct Ctx final : CtxBase {
     // default: measured on B200 (profiles/r2_e_*) the one-pass kernel is SLOWER per level (16.3 / 14.3 / 12.3 us against 11.2 / 9.2 /
     // 9.1 us for the pair, traced): ~1000 predicated instructions per thread in a grid too small to hide them
     bool mg_fused_down = false;
+    bool mv_tile = false;        // INK_CG_MATVEC_TILE=1: k_cg_dir_matvec_tile (shared-memory staging of the direction) instead of k_cg_dir_matvec
     int mg_up_tile = 1;          // INK_MG3_UP_TILE: 0 = k_mg3_up everywhere, 1 = k_mg3_up_tile on levels with >= 2 tiles per SM, 2 = wherever legal
     bool mg_coarsest = true;     // INK_MG3_COARSEST=0: the generic shared-memory tail kernel also when the tail is the coarsest level alone
     bool mg_fuse = true;    // INK_MG3_UNFUSED=1 (debug / A-B): separate residual and full 4x4x4 restriction kernels
@@ -358,6 +359,8 @@ struct Ctx final : CtxBase {
             scan_n.push_back(m);
         }
         for (auto& e : ev) CK(cudaEventCreate(&e));
+        if (const char* e = getenv("INK_CG_MATVEC_TILE")) mv_tile = atoi(e) != 0;
+        CK(cudaFuncSetAttribute((k_cg_dir_matvec_tile<Real>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cg_matvec_tile_smem<Real>()));
         if (const char* e = getenv("INK_K8_TILE")) tile_mode = atoi(e);
         CK(cudaMalloc(&tile_nwork, sizeof(unsigned int)));
         CK(cudaFuncSetAttribute((k_particles_rk2_tile<Real, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, kTileSmemBytes));
@@ -1497,7 +1500,13 @@ struct Ctx final : CtxBase {
         auto iteration_body = [&](int dc) -> int {
             TR("start");
             const ArFold fold1 = make_fold(0, 1, 1);
-            if (vec4()) LAUNCH((k_cg_dir_matvec<Real, 4>), nb, 256, g, S, zsrc, cg_d[dc], cg_d[dc ^ 1], cg_w, hlo, hhi, fold1);
+            if (mv_tile && vec4() && g.n < (1ll << 31)) {   // d' staged once per cell in shared memory (cg.cuh: k_cg_dir_matvec_tile)
+                const int ntx = (g.X + kMvTX - 1) / kMvTX, nty = (g.j1 - g.j0 + kMvTY - 1) / kMvTY, ntz = (g.Z + kMvTZ - 1) / kMvTZ;
+                const unsigned int nbt = (unsigned int)std::min<long long>((long long)ntx * nty * ntz, kCgMaxBlocks);
+                launch_k((k_cg_dir_matvec_tile<Real>), nbt, 256, cg_matvec_tile_smem<Real>(), stream, g, S, (const Real*)zsrc, (const Real*)cg_d[dc], cg_d[dc ^ 1], cg_w, hlo, hhi, fold1, ntx, nty, ntz);
+                ++stats.kernel_launches;
+            }
+            else if (vec4()) LAUNCH((k_cg_dir_matvec<Real, 4>), nb, 256, g, S, zsrc, cg_d[dc], cg_d[dc ^ 1], cg_w, hlo, hhi, fold1);
             else LAUNCH((k_cg_dir_matvec<Real, 1>), nb, 256, g, S, zsrc, cg_d[dc], cg_d[dc ^ 1], cg_w, hlo, hhi, fold1);
             TR("matvec");
             if (dist && !fold1.on) {

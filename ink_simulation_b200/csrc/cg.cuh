@@ -343,6 +343,102 @@ __global__ void __launch_bounds__(256) k_cg_dir_matvec(Grid g, CgScal* S, const 
     }
 }
 
+// ---- k_cg_dir_matvec through a shared-memory tile ------------------------------------------------------------------------
+// The kernel above recomputes d' = r + beta d at the six neighbours of every cell: 14 vector loads per 4 cells through L1 (ncu
+// r1_e: L1/TEX 58 % busy, 3 TB/s for 16 B/cell).  Here a block owns a kMvTX x kMvTY x kMvTZ tile: A) d' for the tile and its
+// one-cell halo (zero outside the GRID: M only couples existing cells; rows of the neighbouring slabs are read like any other),
+// once per cell, into shared memory, the tile's own d' also to global memory; B) w = 6 d' - (six neighbours) from shared
+// memory, <d', w>.  1.6 x 8 B/cell from L2 instead of 7 x 8 B/cell through L1.  Z % 4 == 0.
+constexpr int kMvTX = 8, kMvTY = 8, kMvTZ = 64;
+constexpr int kMvRows = (kMvTX + 2) * (kMvTY + 2);
+constexpr int kMvRow = kMvTZ + 8;                        // [3 pad][k = -1][TZ cells][k = TZ][3 pad]
+template <class Real>
+constexpr size_t cg_matvec_tile_smem() { return (size_t)kMvRows * kMvRow * sizeof(Real); }
+
+template <class Real>
+__global__ void __launch_bounds__(256) k_cg_dir_matvec_tile(Grid g, CgScal* S, const Real* __restrict__ r, const Real* __restrict__ d, Real* __restrict__ dn,
+                                                            Real* __restrict__ w, int halo_lo, int halo_hi, ArFold fold, int ntx, int nty, int ntz) {
+    INK_PDL();
+    if (S->done) return;
+    extern __shared__ __align__(16) unsigned char mv_smem_raw[];
+    Real* xs = reinterpret_cast<Real*>(mv_smem_raw);
+    const Real beta = (S->iters == 0) ? Real(0) : (Real)(S->rz / S->rz_old);
+    const int tid = threadIdx.x;
+    const int sxf = g.sx, syf = (int)g.sy;                   // launcher guarantees X*Y*Z < 2^31
+    double acc = 0;
+    for (int tile = blockIdx.x; tile < ntx * nty * ntz; tile += gridDim.x) {
+        const int tz_ = tile % ntz, txy = tile / ntz, tx_ = txy % ntx, ty_ = txy / ntx;
+        const int fx0 = tx_ * kMvTX, fy0 = g.j0 + ty_ * kMvTY, fz0 = tz_ * kMvTZ;
+        // ---- A: d' on the tile + halo rows (corner rows are nobody's face neighbours)
+        for (int q = tid; q < kMvRows * (kMvTZ / 4); q += 256) {
+            const int zq = q % (kMvTZ / 4), row = q / (kMvTZ / 4), lx = row % (kMvTX + 2), ly = row / (kMvTX + 2);
+            if ((lx == 0 || lx == kMvTX + 1) && (ly == 0 || ly == kMvTY + 1)) continue;
+            const int fi = fx0 - 1 + lx, fj = fy0 - 1 + ly, fk = fz0 + 4 * zq;
+            Pack<Real, 4> v;
+            v.a[0] = v.a[1] = v.a[2] = v.a[3] = Real(0);
+            if (fi >= 0 && fi < g.X && fj >= 0 && fj < g.Y && fk < g.Z) {
+                const int c = fj * syf + fi * sxf + fk;
+                const Pack<Real, 4> rc = ldp<Real, 4>(r + c), dc = ldp<Real, 4>(d + c);
+#pragma unroll
+                for (int a = 0; a < 4; ++a) v.a[a] = rfma(beta, dc.a[a], rc.a[a]);
+                if (lx >= 1 && lx <= kMvTX && ly >= 1 && ly <= kMvTY && fj < g.j1) stp<Real, 4>(dn + c, v);   // this rank's own cells
+            }
+            stp<Real, 4>(xs + row * kMvRow + 4 + 4 * zq, v);
+        }
+        for (int q = tid; q < kMvTX * kMvTY * 2; q += 256) {   // the two z-halo cells of the interior rows
+            const int side = q & 1, col = q >> 1, lx = 1 + col % kMvTX, ly = 1 + col / kMvTX;
+            const int fi = fx0 - 1 + lx, fj = fy0 - 1 + ly, fk = side ? fz0 + kMvTZ : fz0 - 1;
+            Real v = Real(0);
+            if (fi < g.X && fj < g.Y && fk >= 0 && fk < g.Z) { const int c = fj * syf + fi * sxf + fk; v = rfma(beta, d[c], r[c]); }
+            xs[(ly * (kMvTX + 2) + lx) * kMvRow + (side ? 4 + kMvTZ : 3)] = v;
+        }
+        __syncthreads();
+        // ---- B: w = M d' on the tile
+        for (int q = tid; q < kMvTX * kMvTY * (kMvTZ / 4); q += 256) {
+            const int zq = q % (kMvTZ / 4), col = q / (kMvTZ / 4), lx = 1 + col % kMvTX, ly = 1 + col / kMvTX;
+            const int fi = fx0 - 1 + lx, fj = fy0 - 1 + ly, fk = fz0 + 4 * zq;
+            if (fi >= g.X || fj >= g.j1 || fk >= g.Z) continue;
+            const Real* c = xs + (ly * (kMvTX + 2) + lx) * kMvRow + 4 + 4 * zq;
+            const Pack<Real, 4> xc = ldp<Real, 4>(c), xl = ldp<Real, 4>(c - kMvRow), xr = ldp<Real, 4>(c + kMvRow);
+            const Pack<Real, 4> yl = ldp<Real, 4>(c - (kMvTX + 2) * kMvRow), yr = ldp<Real, 4>(c + (kMvTX + 2) * kMvRow);
+            const Real zl = c[-1], zr = c[4];
+            Pack<Real, 4> wc;
+#pragma unroll
+            for (int a = 0; a < 4; ++a) {
+                const Real lo = (a == 0) ? zl : xc.a[a > 0 ? a - 1 : 0], hi = (a == 3) ? zr : xc.a[a < 3 ? a + 1 : 3];
+                // same association as k_cg_dir_matvec: ((x+ + x-) + (y+ + y-) accumulated in that order) + left + right
+                const Real sum = ((xr.a[a] + xl.a[a]) + yr.a[a]) + yl.a[a];
+                wc.a[a] = Real(6) * xc.a[a] - (sum + lo + hi);
+                acc += (double)xc.a[a] * (double)wc.a[a];
+            }
+            stp<Real, 4>(w + (fj * syf + fi * sxf + fk), wc);
+        }
+        __syncthreads();
+    }
+    // multi-GPU: keep the direction current on the neighbour slabs' boundary rows too (see k_cg_dir_matvec)
+    const int nh = halo_lo + halo_hi;
+    if (nh) {
+        const int ZV = g.Z / 4;
+        const long long rowvec = (long long)g.X * ZV;
+        for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < nh * rowvec; t += (long long)gridDim.x * blockDim.x) {
+            const int h = (int)(t / rowvec);
+            const long long rem = t - h * rowvec;
+            const int j = (h == 0 && halo_lo) ? g.j0 - 1 : g.j1;
+            const long long c = (long long)j * g.sy + rem * 4;
+            const Pack<Real, 4> rc = ldp<Real, 4>(r + c), dc = ldp<Real, 4>(d + c);
+            Pack<Real, 4> o;
+#pragma unroll
+            for (int a = 0; a < 4; ++a) o.a[a] = rfma(beta, dc.a[a], rc.a[a]);
+            stp<Real, 4>(dn + c, o);
+        }
+    }
+    double tot;
+    if (block_sum_last(acc, S, 0, tot)) {
+        if (threadIdx.x == 0) { if (S->dist) S->loc[0] = tot; else S->dw = tot; }
+        if (fold.on && threadIdx.x < 32) p2p_fold(S, fold);
+    }
+}
+
 // PRECOND: z = B r is produced by the V-cycle that follows (mg.cuh), which also sets rz / rz_old
 template <class Real, int V, bool PRECOND>
 __global__ void __launch_bounds__(256) k_cg_update(Grid g, CgScal* S, Real* __restrict__ x, Real* __restrict__ r, const Real* __restrict__ d,

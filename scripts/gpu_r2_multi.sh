@@ -5,7 +5,7 @@
 N=${1:-4}
 mkdir -p gpurun_out
 T="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
-timeout 500 $T --master-port 29511 tests/mgpu_check.py > gpurun_out/r2_mgpu_$N.log 2>&1; echo "mgpu rc=$?"; grep -E "^mgpu_check|FAILED|rank [0-9]+:|Error" gpurun_out/r2_mgpu_$N.log | head -20
+timeout 800 $T --master-port 29511 tests/mgpu_check.py > gpurun_out/r2_mgpu_$N.log 2>&1; echo "mgpu rc=$?"; grep -E "^mgpu_check|FAILED|rank [0-9]+:|Error" gpurun_out/r2_mgpu_$N.log | head -20
 INK_MG3_UP_TILE=2 MGPU_CASES=3 timeout 300 $T --master-port 29515 tests/mgpu_check.py > gpurun_out/r2_mgpu_${N}_uptile.log 2>&1; echo "mgpu uptile rc=$?"; grep -E "^mgpu_check|FAILED|rank [0-9]+:|Error" gpurun_out/r2_mgpu_${N}_uptile.log | head -8
 timeout 500 $T --master-port 29512 bench.py --gpus $N --steps 20 --warmup 5 2>gpurun_out/r2_bench_${N}gpu.err | tail -1 > gpurun_out/r2_bench_${N}gpu.json; echo "bench rc=$?"
 python - $N <<PY
