@@ -160,6 +160,7 @@ struct Ctx final : CtxBase {
     // 9.1 us for the pair, traced): ~1000 predicated instructions per thread in a grid too small to hide them
     bool mg_fused_down = false;
     bool mv_tile = false;        // INK_CG_MATVEC_TILE=1: k_cg_dir_matvec_tile (shared-memory staging of the direction) instead of k_cg_dir_matvec
+    int mg_down_tile = 0;        // INK_MG3_DOWN_TILE: 1 = k_mg3_down_tile (residual + restriction in one launch) on levels >= 1, 2 = on every level
     int mg_up_tile = 1;          // INK_MG3_UP_TILE: 0 = k_mg3_up everywhere, 1 = k_mg3_up_tile on levels with >= 2 tiles per SM, 2 = wherever legal
     bool mg_coarsest = true;     // INK_MG3_COARSEST=0: the generic shared-memory tail kernel also when the tail is the coarsest level alone
     bool mg_fuse = true;    // INK_MG3_UNFUSED=1 (debug / A-B): separate residual and full 4x4x4 restriction kernels
@@ -1114,6 +1115,7 @@ struct Ctx final : CtxBase {
         if (const char* e = getenv("INK_MG3_FUSED_DOWN")) mg_fused_down = atoi(e) != 0;
         if (const char* e = getenv("INK_MG3_COARSEST")) mg_coarsest = atoi(e) != 0;
         if (const char* e = getenv("INK_MG3_UP_TILE")) mg_up_tile = atoi(e);
+        if (const char* e = getenv("INK_MG3_DOWN_TILE")) mg_down_tile = atoi(e);
         CK(cudaFuncSetAttribute((k_mg3_up_tile<Real, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mg3_up_tile_smem<Real>()));
         CK(cudaFuncSetAttribute((k_mg3_up_tile<Real, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mg3_up_tile_smem<Real>()));
         if (const char* e = getenv("INK_MG3_UNFUSED")) mg_fuse = (atoi(e) == 0);
@@ -1255,6 +1257,14 @@ struct Ctx final : CtxBase {
             const int l_split = mg_lc >= 1 ? mg_lc : mg_lt;   // levels below l_split: one kernel per pass
             for (int l = 0; l < l_split; ++l) {
                 const MgDims &df = lv[l].d, &dc = lv[l + 1].d;
+                if (mg_down_tile && df.Z % 4 == 0 && (long long)df.X * df.Y * df.Z < (1ll << 31) && (l >= 1 || mg_down_tile == 2)) {
+                    // residual + restriction through a shared-memory tile, one launch (mg_tri.cuh: k_mg3_down_tile)
+                    const int ntx = (dc.X + kDnCX - 1) / kDnCX, nty = (dc.j1 - dc.j0 + kDnCY - 1) / kDnCY, ntz = (dc.Z + kDnCZ - 1) / kDnCZ;
+                    const unsigned int nbt = (unsigned int)std::min<long long>((long long)ntx * nty * ntz, 148 * 32);
+                    LAUNCH((k_mg3_down_tile<Real>), nbt, 256, S, df, dc, rhs(l), lv[l + 1].r, ntx, nty, ntz);
+                    TR(l == 0 ? "down L0" : l == 1 ? "down L1" : "down L2+");
+                    continue;
+                }
                 if (l >= 1 && mg_fused_down) {    // below the finest level a kernel costs its launch, not its traffic: one launch per level
                     LAUNCH((k_mg3_down_fused<Real>), mg_blocks(dc), 256, S, df, dc, rhs(l), lv[l + 1].r);
                     TR(l == 1 ? "down L1" : "down L2+");

@@ -524,6 +524,82 @@ __global__ void __launch_bounds__(256) k_mg3_up_tile(CgScal* S, MgDims df, MgDim
     }
 }
 
+// ---- down pass through a shared-memory tile: residual and full-weighting restriction in ONE launch ----------------------------
+// The kernel pair below (k_mg3_residual_rz_v4 + k_mg3_restrict_xy_v4) stores a z-restricted residual (2 B/cell) and reads it back;
+// on the levels below the finest each of the two launches costs its latency (~4.5 us for < 1 us of work).  Here a block owns a
+// kDnCX x kDnCY x kDnCZ COARSE tile: A) res = r - (omega/6) M r on the 2x fine tile plus its one-cell halo (zero where the fine
+// cell does not exist: exactly the cells the restriction skips), four z-consecutive cells per thread with the vector stencil of
+// mg_lap4, into shared memory; B) one thread per coarse cell gathers its 4x4x4 residuals with the separable weights (1/4, 3/4,
+// 3/4, 1/4).  Same operator as the pair (and as mg3_residual + mg3_restrict), different rounding order.  df.Z % 4 == 0.
+constexpr int kDnCX = 4, kDnCY = 4, kDnCZ = 16;
+constexpr int kDnFX = 2 * kDnCX + 2, kDnFY = 2 * kDnCY + 2, kDnFZ = 2 * kDnCZ;   // fine rows (with halo) and fine z cells (without)
+constexpr int kDnRow = kDnFZ + 8;                        // [3 pad][k = -1][FZ cells][k = FZ][3 pad]: cell k at 4 + k
+template <class Real>
+__global__ void __launch_bounds__(256) k_mg3_down_tile(const CgScal* S, MgDims df, MgDims dc, const Real* __restrict__ r, Real* __restrict__ rc,
+                                                       int ntx, int nty, int ntz) {
+    INK_PDL();
+    if (S->done) return;
+    __shared__ __align__(16) Real rs[kDnFX * kDnFY * kDnRow];
+    const Real w6 = Real(kMgOmega) / Real(6);
+    const int tid = threadIdx.x;
+    const int sxf = df.Z, syf = df.X * df.Z;
+    for (int tile = blockIdx.x; tile < ntx * nty * ntz; tile += gridDim.x) {
+        const int tz_ = tile % ntz, txy = tile / ntz, tx_ = txy % ntx, ty_ = txy / ntx;
+        const int I0 = tx_ * kDnCX, J0 = dc.j0 + ty_ * kDnCY, K0 = tz_ * kDnCZ;
+        const int fx0 = 2 * I0, fy0 = 2 * J0, fz0 = 2 * K0;
+        // ---- A: residual on the fine tile + halo rows, z-quads
+        for (int q = tid; q < kDnFX * kDnFY * (kDnFZ / 4); q += 256) {
+            const int zq = q % (kDnFZ / 4), row = q / (kDnFZ / 4), lx = row % kDnFX, ly = row / kDnFX;
+            const int fi = fx0 - 1 + lx, fj = fy0 - 1 + ly, fk = fz0 + 4 * zq;
+            P4<Real> o = p4_zero<Real>();
+            if (fi >= 0 && fi < df.X && fj >= df.j0 && fj < df.j1 && fk < df.Z) {
+                const long long c = (long long)(fj * syf + fi * sxf + fk);
+                const P4<Real> c4 = ldp<Real, 4>(r + c);
+                Real L[4];
+                mg_lap4<Real>(df, r, c4, fi, fj, fk, c, L);
+#pragma unroll
+                for (int a = 0; a < 4; ++a) o.a[a] = c4.a[a] - w6 * L[a];
+            }
+            stp<Real, 4>(rs + row * kDnRow + 4 + 4 * zq, o);
+        }
+        for (int q = tid; q < kDnFX * kDnFY * 2; q += 256) {   // the two z-halo cells of every row
+            const int side = q & 1, row = q >> 1, lx = row % kDnFX, ly = row / kDnFX;
+            const int fi = fx0 - 1 + lx, fj = fy0 - 1 + ly, fk = side ? fz0 + kDnFZ : fz0 - 1;
+            Real v = Real(0);
+            if (fi >= 0 && fi < df.X && fj >= df.j0 && fj < df.j1 && fk >= 0 && fk < df.Z) {
+                const long long c = mg_idx(df, fi, fj, fk);
+                const Real x0 = r[c];
+                v = x0 - w6 * (Real(6) * x0 - mg_nbr_sum(df, r, fi, fj, fk, c));
+            }
+            rs[row * kDnRow + (side ? 4 + kDnFZ : 3)] = v;
+        }
+        __syncthreads();
+        // ---- B: one coarse cell per thread
+        {
+            const int kc = tid % kDnCZ, ic = (tid / kDnCZ) % kDnCX, jc = tid / (kDnCZ * kDnCX);
+            const int I = I0 + ic, J = J0 + jc, K = K0 + kc;
+            if (I < dc.X && J < dc.j1 && K < dc.Z) {
+                Real acc = Real(0);
+#pragma unroll
+                for (int n = 0; n < 4; ++n) {
+                    const Real wy = (n == 1 || n == 2) ? Real(0.75) : Real(0.25);
+                    Real a = Real(0);
+#pragma unroll
+                    for (int l = 0; l < 4; ++l) {
+                        // fine rows 2I-1+l, 2J-1+n are tile rows (2 ic + l, 2 jc + n); fine z 2K-1 .. 2K+2 start at local index 3 + 2 kc
+                        const Real* p = rs + ((2 * jc + n) * kDnFX + (2 * ic + l)) * kDnRow + 3 + 2 * kc;
+                        const Real zsum = Real(0.25) * (p[0] + p[3]) + Real(0.75) * (p[1] + p[2]);
+                        a += ((l == 1 || l == 2) ? Real(0.75) : Real(0.25)) * zsum;
+                    }
+                    acc += wy * a;
+                }
+                rc[((long long)J * dc.X + I) * dc.Z + K] = acc;
+            }
+        }
+        __syncthreads();
+    }
+}
+
 // ---- fused down-pass for levels with Z % 4 == 0 --------------------------------------------------------------------
 // k_mg3_residual_rz_v4: res = r - (omega/6) M r for 4 z-consecutive cells per thread, restricted along z on the fly:
 //   resz[i, j, K] = 1/4 res[2K-1] + 3/4 res[2K] + 3/4 res[2K+1] + 1/4 res[2K+2]      (layout (Y, X, Z/2), z fastest)

@@ -466,7 +466,8 @@ def test_gpu_tile_particle_kernel_whole_steps(k8_tile_env, oracle_mod):
 
 @pytest.mark.parametrize("dims", [(16, 24, 64), (20, 45, 20), (32, 64, 32), (10, 9, 132), (8, 25, 8)], ids=str)
 @pytest.mark.parametrize("dtype", [np.float32, np.float64], ids=["fp32", "fp64"])
-def test_gpu_up_tile_kernel_is_the_same_preconditioner(oracle_mod, monkeypatch, dims, dtype):
+@pytest.mark.parametrize("switch", ["INK_MG3_UP_TILE", "INK_MG3_DOWN_TILE", "INK_CG_MATVEC_TILE"])
+def test_gpu_up_tile_kernel_is_the_same_preconditioner(oracle_mod, monkeypatch, dims, dtype, switch):
     """k_mg3_up_tile (x' staged through a shared-memory tile) against k_mg3_up (one coarse cell per thread) as the up pass of the
     V-cycle: same operator, different rounding order => the PCG takes the same number of iterations (+-1) and both meet the exact
     DST solution; ragged X / Y, Z below and above the tile length, the default-size and the tiny grids."""
@@ -474,10 +475,10 @@ def test_gpu_up_tile_kernel_is_the_same_preconditioner(oracle_mod, monkeypatch, 
     b = np.random.default_rng(61).normal(size=dims).astype(dtype)
     p_exact, _ = O.poisson_solve(b)
     out = {}
-    for mode in (2, 0):
-        monkeypatch.setenv("INK_MG3_UP_TILE", str(mode))
+    for mode in (2, 0):   # the same holds for the tiled down pass (residual + restriction in one launch) and the tiled CG matvec
+        monkeypatch.setenv(switch, str(mode))
         S = gpu(dims, dtype, cg_rtol=1e-7 if dtype == np.float32 else 1e-12)
-        monkeypatch.delenv("INK_MG3_UP_TILE")
+        monkeypatch.delenv(switch)
         p, res = S.poisson_solve(b)
         out[mode] = (p, S.stats().cg_iters)
         assert util.rel_inf(p, p_exact) < (2e-5 if dtype == np.float32 else 1e-9), (mode, util.rel_inf(p, p_exact))
