@@ -160,6 +160,7 @@ struct Ctx final : CtxBase {
     // 9.1 us for the pair, traced): ~1000 predicated instructions per thread in a grid too small to hide them
     bool mg_fused_down = false;
     bool mv_tile = false;        // INK_CG_MATVEC_TILE=1: k_cg_dir_matvec_tile (shared-memory staging of the direction) instead of k_cg_dir_matvec
+    bool mg_nodone = false;
     int mg_down_tile = 0;        // INK_MG3_DOWN_TILE: 1 = k_mg3_down_tile (residual + restriction in one launch) on levels >= 1, 2 = on every level
     int mg_up_tile = 1;          // INK_MG3_UP_TILE: 0 = k_mg3_up everywhere, 1 = k_mg3_up_tile on levels with >= 2 tiles per SM, 2 = wherever legal
     bool mg_coarsest = true;     // INK_MG3_COARSEST=0: the generic shared-memory tail kernel also when the tail is the coarsest level alone
@@ -1116,6 +1117,7 @@ struct Ctx final : CtxBase {
         if (const char* e = getenv("INK_MG3_COARSEST")) mg_coarsest = atoi(e) != 0;
         if (const char* e = getenv("INK_MG3_UP_TILE")) mg_up_tile = atoi(e);
         if (const char* e = getenv("INK_MG3_DOWN_TILE")) mg_down_tile = atoi(e);
+        if (const char* e = getenv("INK_MG_NODONE")) mg_nodone = atoi(e) != 0;
         CK(cudaFuncSetAttribute((k_mg3_up_tile<Real, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mg3_up_tile_smem<Real>()));
         CK(cudaFuncSetAttribute((k_mg3_up_tile<Real, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mg3_up_tile_smem<Real>()));
         if (const char* e = getenv("INK_MG3_UNFUSED")) mg_fuse = (atoi(e) == 0);
@@ -1253,6 +1255,10 @@ struct Ctx final : CtxBase {
     int mg_vcycle(const Real* r0) {
         auto rhs = [&](int l) -> const Real* { return l == 0 ? r0 : lv[l].r; };
         if (mg_tri) {
+            // INK_MG_NODONE=1: the V-cycle kernels that touch S only for the `done` early exit get S = nullptr and skip that dependent
+            // load (~0.5 us in front of every one of ~11 short kernels per iteration); after convergence they then recompute z from
+            // an unchanged r instead of exiting — harmless (x, r and the scalars are guarded by the CG kernels and the FINAL up kernel)
+            const CgScal* Sd = mg_nodone ? nullptr : S;
             // V(1,1), trilinear transfer: 3 launches per global level (residual, restrict | up), xb = residual scratch
             const int l_split = mg_lc >= 1 ? mg_lc : mg_lt;   // levels below l_split: one kernel per pass
             for (int l = 0; l < l_split; ++l) {
@@ -1261,30 +1267,30 @@ struct Ctx final : CtxBase {
                     // residual + restriction through a shared-memory tile, one launch (mg_tri.cuh: k_mg3_down_tile)
                     const int ntx = (dc.X + kDnCX - 1) / kDnCX, nty = (dc.j1 - dc.j0 + kDnCY - 1) / kDnCY, ntz = (dc.Z + kDnCZ - 1) / kDnCZ;
                     const unsigned int nbt = (unsigned int)std::min<long long>((long long)ntx * nty * ntz, 148 * 32);
-                    LAUNCH((k_mg3_down_tile<Real>), nbt, 256, S, df, dc, rhs(l), lv[l + 1].r, ntx, nty, ntz);
+                    LAUNCH((k_mg3_down_tile<Real>), nbt, 256, Sd, df, dc, rhs(l), lv[l + 1].r, ntx, nty, ntz);
                     TR(l == 0 ? "down L0" : l == 1 ? "down L1" : "down L2+");
                     continue;
                 }
                 if (l >= 1 && mg_fused_down) {    // below the finest level a kernel costs its launch, not its traffic: one launch per level
-                    LAUNCH((k_mg3_down_fused<Real>), mg_blocks(dc), 256, S, df, dc, rhs(l), lv[l + 1].r);
+                    LAUNCH((k_mg3_down_fused<Real>), mg_blocks(dc), 256, Sd, df, dc, rhs(l), lv[l + 1].r);
                     TR(l == 1 ? "down L1" : "down L2+");
                     continue;
                 }
                 if (df.Z % 4 == 0 && mg_fuse) {   // residual + z-restriction fused (xb holds the half-size z-restricted residual)
                     const long long nv = (long long)df.X * (df.j1 - df.j0) * (df.Z / 4);
-                    LAUNCH((k_mg3_residual_rz_v4<Real>), (unsigned int)std::min<long long>(kMgBlocks, std::max<long long>(1, (nv + 255) / 256)), 256, S, df, rhs(l), lv[l].xb);
+                    LAUNCH((k_mg3_residual_rz_v4<Real>), (unsigned int)std::min<long long>(kMgBlocks, std::max<long long>(1, (nv + 255) / 256)), 256, Sd, df, rhs(l), lv[l].xb);
                     if (dc.Z % 4 == 0) {
                         const long long nc4 = (long long)dc.X * (dc.j1 - dc.j0) * (dc.Z / 4);
-                        LAUNCH((k_mg3_restrict_xy_v4<Real>), (unsigned int)std::min<long long>(kMgBlocks, std::max<long long>(1, (nc4 + 255) / 256)), 256, S, df, dc, lv[l].xb, lv[l + 1].r);
-                    } else LAUNCH((k_mg3_restrict_xy<Real>), mg_blocks(dc), 256, S, df, dc, lv[l].xb, lv[l + 1].r);
+                        LAUNCH((k_mg3_restrict_xy_v4<Real>), (unsigned int)std::min<long long>(kMgBlocks, std::max<long long>(1, (nc4 + 255) / 256)), 256, Sd, df, dc, lv[l].xb, lv[l + 1].r);
+                    } else LAUNCH((k_mg3_restrict_xy<Real>), mg_blocks(dc), 256, Sd, df, dc, lv[l].xb, lv[l + 1].r);
                     TR(l == 0 ? "down L0" : l == 1 ? "down L1" : "down L2+");
                     continue;
                 }
                 if (df.Z % 4 == 0) {
                     const long long nv = (long long)df.X * (df.j1 - df.j0) * (df.Z / 4);
-                    LAUNCH((k_mg3_residual_v4<Real>), (unsigned int)std::min<long long>(kMgBlocks, std::max<long long>(1, (nv + 255) / 256)), 256, S, df, rhs(l), lv[l].xb);
-                } else LAUNCH((k_mg3_residual<Real>), mg_blocks(df), 256, S, df, rhs(l), lv[l].xb);
-                LAUNCH((k_mg3_restrict<Real>), mg_blocks(dc), 256, S, df, dc, lv[l].xb, lv[l + 1].r);
+                    LAUNCH((k_mg3_residual_v4<Real>), (unsigned int)std::min<long long>(kMgBlocks, std::max<long long>(1, (nv + 255) / 256)), 256, Sd, df, rhs(l), lv[l].xb);
+                } else LAUNCH((k_mg3_residual<Real>), mg_blocks(df), 256, Sd, df, rhs(l), lv[l].xb);
+                LAUNCH((k_mg3_restrict<Real>), mg_blocks(dc), 256, Sd, df, dc, lv[l].xb, lv[l + 1].r);
             }
             if (mg_lc >= 1) {   // levels mg_lc .. mg_lt (down, tail, up) in one persistent launch
                 Mg3CoarseArgs<Real> A{};
@@ -1301,7 +1307,7 @@ struct Ctx final : CtxBase {
                 const MgDims& d = lv[mg_lt].d;
                 const long long off = (long long)d.j0 * d.X * d.Z;
                 if (mg_coarsest && mg_tail.nlev == 1 && !mg_tail.final_dot && (long long)d.X * (d.j1 - d.j0) * d.Z <= kMg3CoarsestCells)
-                    launch_k(k_mg3_coarsest<Real>, 1, kMg3CoarsestThreads, 0, stream, S, d, lv[mg_lt].s, rhs(mg_lt) + off, lv[mg_lt].xa + off);
+                    launch_k(k_mg3_coarsest<Real>, 1, kMg3CoarsestThreads, 0, stream, Sd, d, lv[mg_lt].s, rhs(mg_lt) + off, lv[mg_lt].xa + off);
                 else launch_k(k_mg3_tail<Real>, 1, kMgTailThreads, mg_tail_smem, stream, S, mg_tail, rhs(mg_lt) + off, lv[mg_lt].xa + off);
                 ++stats.kernel_launches;
                 TR("tail");
@@ -1318,11 +1324,11 @@ struct Ctx final : CtxBase {
                 if (mg_up_tile && df.Z % 4 == 0 && (long long)df.X * df.Y * df.Z < (1ll << 31) && ntile >= (mg_up_tile == 2 ? 1 : 2 * kSMs)) {
                     const unsigned int nb = (unsigned int)std::min<long long>(ntile, kCgMaxBlocks);
                     if (l == 0) launch_k((k_mg3_up_tile<Real, true>), nb, 256, mg3_up_tile_smem<Real>(), stream, S, df, dc, lv[l].s, rhs(l), (const Real*)lv[l + 1].xa, lv[l].xa, dot0, dot1, ntx, nty, ntz);
-                    else launch_k((k_mg3_up_tile<Real, false>), nb, 256, mg3_up_tile_smem<Real>(), stream, S, df, dc, lv[l].s, rhs(l), (const Real*)lv[l + 1].xa, lv[l].xa, 0, 0, ntx, nty, ntz);
+                    else launch_k((k_mg3_up_tile<Real, false>), nb, 256, mg3_up_tile_smem<Real>(), stream, (CgScal*)Sd, df, dc, lv[l].s, rhs(l), (const Real*)lv[l + 1].xa, lv[l].xa, 0, 0, ntx, nty, ntz);
                     ++stats.kernel_launches;
                 }
                 else if (l == 0) LAUNCH((k_mg3_up<Real, true>), std::min<unsigned int>(ub, kCgMaxBlocks), 256, S, df, dc, lv[l].s, rhs(l), lv[l + 1].xa, lv[l].xa, dot0, dot1);
-                else LAUNCH((k_mg3_up<Real, false>), ub, 256, S, df, dc, lv[l].s, rhs(l), lv[l + 1].xa, lv[l].xa, 0, 0);
+                else LAUNCH((k_mg3_up<Real, false>), ub, 256, (CgScal*)Sd, df, dc, lv[l].s, rhs(l), lv[l + 1].xa, lv[l].xa, 0, 0);
                 TR(l == 0 ? "up L0" : l == 1 ? "up L1" : "up L2+");
             }
             CK(cudaGetLastError());

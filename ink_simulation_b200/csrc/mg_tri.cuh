@@ -338,14 +338,14 @@ INK_HD double mg3_up(const MgDims& df, const MgDims& dc, Real s, const Real* __r
 template <class Real>
 __global__ void __launch_bounds__(256) k_mg3_residual(const CgScal* S, MgDims d, const Real* __restrict__ r, Real* __restrict__ res) {
     INK_PDL();
-    if (S->done) return;
+    if (S != nullptr && S->done) return;
     mg3_residual<Real>(d, r, res, (long long)blockIdx.x * blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x);
 }
 // Z % 4 == 0: one thread per 4 z-consecutive cells, 128-bit accesses (same arithmetic per cell)
 template <class Real>
 __global__ void __launch_bounds__(256) k_mg3_residual_v4(const CgScal* S, MgDims d, const Real* __restrict__ r, Real* __restrict__ res) {
     INK_PDL();
-    if (S->done) return;
+    if (S != nullptr && S->done) return;
     const Real w6 = Real(kMgOmega) / Real(6);
     int i, j, k; long long c;
     for (unsigned int t = blockIdx.x * blockDim.x + threadIdx.x; mg_vec_cell(d, t, i, j, k, c); t += gridDim.x * blockDim.x) {
@@ -361,7 +361,7 @@ __global__ void __launch_bounds__(256) k_mg3_residual_v4(const CgScal* S, MgDims
 template <class Real>
 __global__ void __launch_bounds__(256) k_mg3_restrict(const CgScal* S, MgDims df, MgDims dc, const Real* __restrict__ res, Real* __restrict__ rc) {
     INK_PDL();
-    if (S->done) return;
+    if (S != nullptr && S->done) return;
     mg3_restrict<Real>(df, dc, res, rc, (long long)blockIdx.x * blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x);
 }
 // FINAL: level 0 — also produces <r, z> for CG (rz_old <- rz, rz <- <r,z>)
@@ -369,7 +369,7 @@ template <class Real, bool FINAL>
 __global__ void __launch_bounds__(256, 3) k_mg3_up(CgScal* S, MgDims df, MgDims dc, Real s, const Real* __restrict__ r, const Real* __restrict__ e,
                                                 Real* __restrict__ z, int dj0, int dj1) {
     INK_PDL();
-    if (S->done) return;
+    if (S != nullptr && S->done) return;   // S may be nullptr for the non-FINAL levels (INK_MG_NODONE)
     const double acc = mg3_up<Real>(df, dc, s, r, e, z, (long long)blockIdx.x * blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x, dj0, dj1);
     if (FINAL) {
         double tot;
@@ -412,7 +412,7 @@ template <class Real, bool FINAL>
 __global__ void __launch_bounds__(256) k_mg3_up_tile(CgScal* S, MgDims df, MgDims dc, Real s, const Real* __restrict__ r, const Real* __restrict__ e,
                                                      Real* __restrict__ z, int dj0, int dj1, int ntx, int nty, int ntz) {
     INK_PDL();
-    if (S->done) return;
+    if (S != nullptr && S->done) return;   // S may be nullptr for the non-FINAL levels (INK_MG_NODONE)
     extern __shared__ __align__(16) unsigned char up_smem_raw[];
     Real* xs = reinterpret_cast<Real*>(up_smem_raw);            // x' rows
     Real* es = xs + kUpRows * kUpRow;                           // coarse values
@@ -538,7 +538,7 @@ template <class Real>
 __global__ void __launch_bounds__(256) k_mg3_down_tile(const CgScal* S, MgDims df, MgDims dc, const Real* __restrict__ r, Real* __restrict__ rc,
                                                        int ntx, int nty, int ntz) {
     INK_PDL();
-    if (S->done) return;
+    if (S != nullptr && S->done) return;
     __shared__ __align__(16) Real rs[kDnFX * kDnFY * kDnRow];
     const Real w6 = Real(kMgOmega) / Real(6);
     const int tid = threadIdx.x;
@@ -647,14 +647,14 @@ __device__ __forceinline__ void mg3_residual_rz_v4_dev(const MgDims& d, const Re
 template <class Real>
 __global__ void __launch_bounds__(256) k_mg3_residual_rz_v4(const CgScal* S, MgDims d, const Real* __restrict__ r, Real* __restrict__ resz) {
     INK_PDL();
-    if (S->done) return;
+    if (S != nullptr && S->done) return;
     mg3_residual_rz_v4_dev<Real>(d, r, resz, blockIdx.x * blockDim.x + threadIdx.x, gridDim.x * blockDim.x);
 }
 // rc[I,J,K] = sum over the 4x4 fine columns (2I-1..2I+2, 2J-1..2J+2) of wx wy resz[.,.,K]
 template <class Real>
 __global__ void __launch_bounds__(256) k_mg3_restrict_xy(const CgScal* S, MgDims df, MgDims dc, const Real* __restrict__ resz, Real* __restrict__ rc) {
     INK_PDL();
-    if (S->done) return;
+    if (S != nullptr && S->done) return;
     INK_MG_CELL_LOOP(dc, (long long)blockIdx.x * blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x) {
         INK_MG_DECODE(dc)
         Real acc = Real(0);
@@ -708,14 +708,14 @@ __device__ __forceinline__ void mg3_restrict_xy_v4_dev(const MgDims& df, const M
 template <class Real>
 __global__ void __launch_bounds__(256) k_mg3_restrict_xy_v4(const CgScal* S, MgDims df, MgDims dc, const Real* __restrict__ resz, Real* __restrict__ rc) {
     INK_PDL();
-    if (S->done) return;
+    if (S != nullptr && S->done) return;
     mg3_restrict_xy_v4_dev<Real>(df, dc, resz, rc, blockIdx.x * blockDim.x + threadIdx.x, gridDim.x * blockDim.x);
 }
 
 template <class Real>
 __global__ void __launch_bounds__(256) k_mg3_down_fused(const CgScal* S, MgDims df, MgDims dc, const Real* __restrict__ r, Real* __restrict__ rc) {
     INK_PDL();
-    if (S->done) return;
+    if (S != nullptr && S->done) return;
     mg3_down_fused<Real>(df, dc, r, rc, (long long)blockIdx.x * blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x);
 }
 
@@ -728,7 +728,7 @@ constexpr int kMg3CoarsestThreads = 1024;
 template <class Real>
 __global__ void __launch_bounds__(kMg3CoarsestThreads) k_mg3_coarsest(const CgScal* S, MgDims d, Real s, const Real* __restrict__ rin, Real* __restrict__ xout) {
     INK_PDL();
-    if (S->done) return;
+    if (S != nullptr && S->done) return;
     __shared__ Real xs[2][kMg3CoarsestCells + 1];
     const int X = d.X, Z = d.Z, rows = d.j1 - d.j0, n = X * rows * Z;   // rin / xout already point at the slab's first cell
     const Real cj = Real(kMgOmega) / (Real(6) * s);
