@@ -1278,7 +1278,9 @@ struct Ctx final : CtxBase {
                 }
                 if (df.Z % 4 == 0 && mg_fuse) {   // residual + z-restriction fused (xb holds the half-size z-restricted residual)
                     const long long nv = (long long)df.X * (df.j1 - df.j0) * (df.Z / 4);
-                    LAUNCH((k_mg3_residual_rz_v4<Real>), (unsigned int)std::min<long long>(kMgBlocks, std::max<long long>(1, (nv + 255) / 256)), 256, Sd, df, rhs(l), lv[l].xb);
+                    const unsigned int nbr = (unsigned int)std::min<long long>(kMgBlocks, std::max<long long>(1, (nv + 255) / 256));
+                    if (df.Z / 4 > 32) LAUNCH((k_mg3_residual_rz_v4_blk<Real>), nbr, 256, Sd, df, rhs(l), lv[l].xb);   // rows longer than a warp of quads
+                    else LAUNCH((k_mg3_residual_rz_v4<Real>), nbr, 256, Sd, df, rhs(l), lv[l].xb);
                     if (dc.Z % 4 == 0) {
                         const long long nc4 = (long long)dc.X * (dc.j1 - dc.j0) * (dc.Z / 4);
                         LAUNCH((k_mg3_restrict_xy_v4<Real>), (unsigned int)std::min<long long>(kMgBlocks, std::max<long long>(1, (nc4 + 255) / 256)), 256, Sd, df, dc, lv[l].xb, lv[l + 1].r);

@@ -439,6 +439,7 @@ __global__ void __launch_bounds__(256) k_mg3_up_tile(CgScal* S, MgDims df, MgDim
         // ---- A: x' on the tile + halo rows, one z-quad per thread and pass
         for (int q = tid; q < kUpRows * (kUpTZ / 4); q += 256) {
             const int zq = q % (kUpTZ / 4), row = q / (kUpTZ / 4), lx = row % (kUpTX + 2), ly = row / (kUpTX + 2);
+            if ((lx == 0 || lx == kUpTX + 1) && (ly == 0 || ly == kUpTY + 1)) continue;   // corner rows are nobody's face neighbours
             const int fi = fx0 - 1 + lx, fj = fy0 - 1 + ly, fk = fz0 + 4 * zq;
             P4<Real> xp = p4_zero<Real>();
             if (fi >= 0 && fi < df.X && fj >= df.j0 && fj < df.j1 && fk < df.Z) {
@@ -447,24 +448,25 @@ __global__ void __launch_bounds__(256) k_mg3_up_tile(CgScal* S, MgDims df, MgDim
                 mg3_donors(fi, cx0, xm, xo);
                 mg3_donors(fj, cy0, ym, yo);
                 const int lk = 2 * zq;                           // local coarse index of K - 1, K = fk / 2
-                Real t[2][2][4];                                 // [x donor][y donor][fine cell]: z-interpolated columns
-#pragma unroll
-                for (int a = 0; a < 2; ++a)
-#pragma unroll
-                    for (int b = 0; b < 2; ++b) {
-                        const Real* col = es + ((b ? yo : ym) * kUpCX + (a ? xo : xm)) * kUpCRow + lk;
-                        const Pack<Real, 2> v01 = ldp<Real, 2>(col), v23 = ldp<Real, 2>(col + 2);
-                        t[a][b][0] = hd_fma(Real(3), v01.a[1], v01.a[0]);
-                        t[a][b][1] = hd_fma(Real(3), v01.a[1], v23.a[0]);
-                        t[a][b][2] = hd_fma(Real(3), v23.a[0], v01.a[1]);
-                        t[a][b][3] = hd_fma(Real(3), v23.a[0], v23.a[1]);
-                    }
-#pragma unroll
-                for (int m = 0; m < 4; ++m) {
-                    const Real um = hd_fma(Real(3), t[0][0][m], t[0][1][m]);   // main x donor: 3 * main y + other y
-                    const Real uo = hd_fma(Real(3), t[1][0][m], t[1][1][m]);
-                    xp.a[m] = hd_fma(sc, hd_fma(Real(3), um, uo), cj * rq.a[m]);
+                // x-y combination FIRST, on the four coarse z values (9 mm + 3 mo + 3 om + oo per value: 12 FMAs), then the z
+                // interpolation of the four fine cells (4 FMAs): 16 FMAs per quad instead of 28 for z-first
+                Real g[4];
+                {
+                    const Real* cmm = es + (ym * kUpCX + xm) * kUpCRow + lk;
+                    const Real* cmo = es + (yo * kUpCX + xm) * kUpCRow + lk;   // main x, other y
+                    const Real* com = es + (ym * kUpCX + xo) * kUpCRow + lk;
+                    const Real* coo = es + (yo * kUpCX + xo) * kUpCRow + lk;
+                    const Pack<Real, 2> a01 = ldp<Real, 2>(cmm), a23 = ldp<Real, 2>(cmm + 2), b01 = ldp<Real, 2>(cmo), b23 = ldp<Real, 2>(cmo + 2);
+                    const Pack<Real, 2> c01 = ldp<Real, 2>(com), c23 = ldp<Real, 2>(com + 2), d01 = ldp<Real, 2>(coo), d23 = ldp<Real, 2>(coo + 2);
+                    g[0] = hd_fma(Real(3), hd_fma(Real(3), a01.a[0], b01.a[0]), hd_fma(Real(3), c01.a[0], d01.a[0]));
+                    g[1] = hd_fma(Real(3), hd_fma(Real(3), a01.a[1], b01.a[1]), hd_fma(Real(3), c01.a[1], d01.a[1]));
+                    g[2] = hd_fma(Real(3), hd_fma(Real(3), a23.a[0], b23.a[0]), hd_fma(Real(3), c23.a[0], d23.a[0]));
+                    g[3] = hd_fma(Real(3), hd_fma(Real(3), a23.a[1], b23.a[1]), hd_fma(Real(3), c23.a[1], d23.a[1]));
                 }
+                xp.a[0] = hd_fma(sc, hd_fma(Real(3), g[1], g[0]), cj * rq.a[0]);
+                xp.a[1] = hd_fma(sc, hd_fma(Real(3), g[1], g[2]), cj * rq.a[1]);
+                xp.a[2] = hd_fma(sc, hd_fma(Real(3), g[2], g[1]), cj * rq.a[2]);
+                xp.a[3] = hd_fma(sc, hd_fma(Real(3), g[2], g[3]), cj * rq.a[3]);
             }
             stp<Real, 4>(xs + row * kUpRow + 4 + 4 * zq, xp);
         }
@@ -649,6 +651,46 @@ __global__ void __launch_bounds__(256) k_mg3_residual_rz_v4(const CgScal* S, MgD
     INK_PDL();
     if (S != nullptr && S->done) return;
     mg3_residual_rz_v4_dev<Real>(d, r, resz, blockIdx.x * blockDim.x + threadIdx.x, gridDim.x * blockDim.x);
+}
+// Rows longer than one warp of quads (Z > 128): the two residuals a thread lacks come from its neighbours THROUGH SHARED MEMORY (a block covers 256 consecutive
+// quads, i.e. whole rows whenever Z/4 divides 256): no warp-edge recomputation.  ncu at 256^3 (profiles/r2_l_c4_level0_kernels.txt)
+// showed the shuffle version issue-bound — 74 % issue slots, 233 warp instructions per warp of quads — because with Z/4 = 64 every
+// warp's lane 0 or lane 31 recomputed a 7-point residual in a divergent branch.  Only a block-edge thread in the middle of a row
+// (Z > 1024) still recomputes.  Measured: down L0 57 -> 47 us at 256^3; on rows of <= 32 quads the shuffle kernel above never
+// recomputes and is faster (no block barriers), so the launcher picks by row length.
+template <class Real>
+__global__ void __launch_bounds__(256) k_mg3_residual_rz_v4_blk(const CgScal* S, MgDims d, const Real* __restrict__ r, Real* __restrict__ resz) {
+    INK_PDL();
+    if (S != nullptr && S->done) return;
+    __shared__ Real edge[2][256];
+    const Real w6 = Real(kMgOmega) / Real(6);
+    const unsigned int ZV = (unsigned int)d.Z >> 2;
+    const unsigned int tot = (unsigned int)(d.j1 - d.j0) * (unsigned int)d.X * ZV;
+    const unsigned int tid = threadIdx.x;
+    for (unsigned int base = blockIdx.x * 256u; base < tot; base += gridDim.x * 256u) {   // block-uniform trip count
+        int i = 0, j = 0, k = 0; long long c = 0;
+        Real res[4] = {Real(0), Real(0), Real(0), Real(0)};
+        const bool act = mg_vec_cell(d, base + tid, i, j, k, c);
+        if (act) {
+            const P4<Real> rc = ldp<Real, 4>(r + c);
+            Real L[4];
+            mg_lap4<Real>(d, r, rc, i, j, k, c, L);
+#pragma unroll
+            for (int a = 0; a < 4; ++a) res[a] = rc.a[a] - w6 * L[a];
+        }
+        edge[0][tid] = res[0]; edge[1][tid] = res[3];
+        __syncthreads();
+        if (act) {
+            Real left = Real(0), right = Real(0);
+            if (k > 0) left = (tid > 0) ? edge[1][tid - 1] : mg3_res_at<Real>(d, r, i, j, k - 1);          // quad t - 1 is the same row
+            if (k + 4 < d.Z) right = (tid < 255u) ? edge[0][tid + 1] : mg3_res_at<Real>(d, r, i, j, k + 4);
+            Pack<Real, 2> o;
+            o.a[0] = Real(0.25) * (left + res[2]) + Real(0.75) * (res[0] + res[1]);
+            o.a[1] = Real(0.25) * (res[1] + right) + Real(0.75) * (res[2] + res[3]);
+            stp<Real, 2>(resz + (c >> 1), o);   // c = row * Z + k, Z and k even: (row * Z/2 + k/2)
+        }
+        __syncthreads();
+    }
 }
 // rc[I,J,K] = sum over the 4x4 fine columns (2I-1..2I+2, 2J-1..2J+2) of wx wy resz[.,.,K]
 template <class Real>
