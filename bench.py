@@ -757,7 +757,7 @@ def main():
     torch.cuda.empty_cache()
     if strict_pos is not None:
         # the bit-exact arithmetic (the ABI default, what the parity suite pins) on the same workload, beside the headline
-        blk = nested_solve_block(args, H, args.config, args.strong, max(args.steps, 50), arith="strict", particles_from=strict_pos)
+        blk = nested_solve_block(args, H, args.config, args.strong, n_solves, arith="strict", particles_from=strict_pos)   # same protocol: same number of timed solves
         line["strict"] = {k: blk[k] for k in ("arith", "steps", "ms_per_step", "particle_updates_per_s", "cell_steps_per_s", "cg_iters", "phase_ms_last_step")}
         del strict_pos
         torch.cuda.empty_cache()
