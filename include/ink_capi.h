@@ -72,8 +72,9 @@ typedef struct ink_stats {
     int32_t advect_skipped; /* 1 if the convection phase was proven to be the identity and skipped */
     int64_t steps;          /* ink_step calls so far */
     int64_t resorts;        /* particle re-binnings so far */
-    int64_t kernel_launches;/* kernels launched by this ctx so far */
-    int32_t cg_converged;   /* 1: the last pressure solve met cg_rtol; 0: it stopped at cg_max_iters (ink_step then returns an error) */
+    int64_t kernel_launches;/* kernels executed for this ctx so far (kernel nodes of replayed CUDA graphs included) */
+    int32_t cg_converged;   /* 1: the last pressure solve met cg_rtol; 0: it stopped at cg_max_iters (no error: callers that fix the
+                               iteration count rely on it).  A NON-FINITE residual is an error: ink_step / ink_pressure return non-zero */
     int32_t graph_launches; /* CUDA-graph launches by this ctx so far (each replays one captured PCG iteration) */
 } ink_stats;
 
