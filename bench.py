@@ -688,12 +688,14 @@ def main():
     alg_k8 = (9 * rbytes) * n_local + 3 * rbytes * ncell
     traffic_note = None
     traffic = None
+    pcg_iter_traffic = None
     if world == 1 and args.config == "c3" and args.dtype == "f32":
         try:
             with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
                 tj = json.load(f)
             traffic = tj.get(f"k_particles_rk2:{args.config}:{args.arith}:{args.dtype}")
             traffic_note = tj.get("_capture", "ncu --set full capture (profiles/), not this run")
+            pcg_iter_traffic = tj.get("pcg_iteration:c3:f32")
         except Exception:
             pass
     per_kernel = [{"kernel": f"k_particles_rk2<{args.dtype},{args.arith}>", "bound": "hbm", "achieved": alg_k8 / max(part_ms, 1e-9) / 1e6,
@@ -710,7 +712,10 @@ def main():
     alg_p = vec_passes * rbytes * ncl
     roof = {"kernel": "pressure phase: PCG (k_cg_dir_matvec, k_cg_update, k_mg3_* V-cycle) + RHS + gradient subtract", "bound": "hbm",
             "achieved": alg_p / max(cg_ms, 1e-9) / 1e6, "peak": peak, "unit": "GB/s", "frac": alg_p / max(cg_ms, 1e-9) / 1e6 / peak,
-            "traffic": None, "peak_source": peak_src, "alg_bytes": alg_p, "ms": cg_ms, "cg_iters": last_iters,
+            "traffic": (pcg_iter_traffic * max(last_iters, 0)) if pcg_iter_traffic else None,
+            "traffic_source": "DRAM bytes of one PCG iteration (ncu --set full, profiles/r2_h_top_kernels.txt, C3 on one GPU; not this run) x iterations: "
+                              "below the algorithmic bytes because most of the working set stays in L2" if pcg_iter_traffic else None,
+            "peak_source": peak_src, "alg_bytes": alg_p, "ms": cg_ms, "cg_iters": last_iters,
             "share_of_step": cg_ms / max(sum(phase_acc.values()), 1e-9),
             "survey_8d": {"bytes_per_cell_per_iter": 44, "frac": (44 * last_iters + 44) * (rbytes / 4) * ncl / max(cg_ms, 1e-9) / 1e6 / peak},
             "per_kernel": per_kernel}
