@@ -3,12 +3,15 @@
   (2) the CPU oracle on fresh seeded inputs, including shapes the reference cannot take (X != Z, Q1).
 fp32 + strict arithmetic is BIT-EXACT for every phase but the Poisson solve; tolerances for the rest are the
 north_star's (1e-5 field-relative on the projected velocity, 1e-6 relative on particle positions)."""
+import os
+
 import numpy as np
 import pytest
 
 import parity
 import util
 
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 pytestmark = pytest.mark.gpu
 
 
@@ -531,3 +534,14 @@ def test_gpu_bench_solver_tolerance_meets_the_north_star(oracle_mod, dims):
         O.vorticity(dt); S.vorticity(dt)
         O.particles(dt); S.particles(dt)
     S.close()
+
+
+def test_gpu_every_kernel_variant_runs_on_ragged_grids():
+    """scripts/sanitize_r2.py: whole steps with wild particles on small ragged grids under every opt-in kernel switch of round 2
+    (tiled up / down / matvec, K8 tile, one-pass down, cluster coarse kernel) and the device seeders; every run must stay finite
+    (ink_check_finite).  Own process: the switches are environment variables read when a context is created."""
+    import subprocess
+    import sys
+
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "sanitize_r2.py")], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and "sanitize_r2: done" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
