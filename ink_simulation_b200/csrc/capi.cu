@@ -1131,7 +1131,9 @@ struct Ctx final : CtxBase {
         if (world > 1) {
             int min_rows = g.Y;
             for (int r = 0; r < world; ++r) min_rows = std::min(min_rows, slab_lo[r + 1] - slab_lo[r]);
-            ovl = std::max(1, std::min(8, min_rows / 2));
+            int ovl_max = 8;   // INK_SCHWARZ_OVL: overlap rows of the Schwarz preconditioner (always <= half the thinnest slab)
+            if (const char* e = getenv("INK_SCHWARZ_OVL")) ovl_max = std::max(1, atoi(e));
+            ovl = std::max(1, std::min(ovl_max, min_rows / 2));
             if (rank > 0) { je0 = g.j0 - ovl; dot0 = g.j0 + ovl; }
             if (rank + 1 < world) { je1 = g.j1 + ovl; dot1 = g.j1 - ovl; }
             // sqrt of the linear partition of unity across each 2*ovl-row band (two ranks' weights sum to 1 on every row)
