@@ -165,6 +165,39 @@ int  ink_get_stats(ink_ctx* c, ink_stats* out);
 /* Device-time of every phase of the last ink_step in ms: dt, advect, forces, viscosity, pressure, vorticity, particles, resort */
 int  ink_get_phase_ms(ink_ctx* c, float out[8]);
 
+/* ---- for callers that cannot allocate device memory --------------------------------------------------------------
+ * This entry point has no counterpart in the reference (which has no device at all); it is ink_check_finite's reduction
+ * without an ink_ctx.  Every other call needs a context, and ink_create cudaMallocs the whole simulation state.  That
+ * rules out a host application which handed all of HBM to its own arena at start-up (cudaMalloc fails there), and a
+ * frame loop that may not stall (cudaMalloc and cudaFree synchronise the device and hold up every other stream of the
+ * process).  Such a host keeps grid and particles in its own buffers; this call inspects them in place and allocates
+ * nothing: no cudaMalloc / cudaFree, no pinned memory, no library that allocates behind the scenes.
+ *
+ *   x, y, z      DEVICE pointers (memory of the CURRENT device): element t is (x[t*stride], y[t*stride], z[t*stride]).
+ *                stride = 1: three dense arrays (a velocity field).  stride = 3 with (p, p + 1, p + 2): one N x 3 array,
+ *                the layout of Particle::position / ::velocity used by ink_set_particles.
+ *   n            number of elements, 0 <= n <= INK_NOALLOC_MAX_N; anything larger is refused (return 2): split the range.
+ *   dtype        32 = float, 64 = double.
+ *   check_norm   1: also count elements whose norm() is not < 10000 (velocities); 0: positions (NaN / Inf test only).
+ *   counts_dev   DEVICE pointer to two uint64, OVERWRITTEN (not added to): [0] = elements with a NaN / Inf component,
+ *                [1] = elements failing the norm test (0 when check_norm = 0).  Same counting rules as ink_check_finite.
+ *   cuda_stream  the cudaStream_t (of the current device) to run on, NULL = the legacy default stream.  The call only
+ *                enqueues: the counts are there when work queued on that stream before them has finished.
+ *
+ * The kernel's only scratch memory is a file-scope device array of 256 B + 256 KiB inside the library image (one slot
+ * of partial counts per block of 8192 elements, hence the limit).  Every GPU on which the library's kernels get
+ * loaded holds one copy of it until the process exits.  What follows from that:
+ *   - the FIRST call on each device looks up that device's copy (cudaGetSymbolAddress) with the caller's current device;
+ *     make that first call during set-up, and in any case before a stream capture is begun on the stream;
+ *   - all calls on one device share the array.  Two calls whose kernels can run at the same time on the GPU (different
+ *     streams, or different host threads on different streams) race on it and give wrong counts; calls on ONE stream,
+ *     or otherwise ordered one after the other, are safe.  Nothing is carried from call to call: the block ticket is
+ *     cleared on the stream before each launch, and every slot is written before it is read.
+ * Returns 0, or non-zero with a message from ink_last_error(NULL) on the calling thread. */
+#define INK_NOALLOC_MAX_N 268435456LL   /* 2^28 elements per call */
+int  ink_check_finite_noalloc(const void* x, const void* y, const void* z, int64_t n, int64_t stride, int dtype, int check_norm,
+                              uint64_t* counts_dev, void* cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -11,6 +11,7 @@ LIB_PATH = os.path.join(_HERE, "libinkb200.so")
 ARITH_STRICT, ARITH_FAST = 0, 1
 FIELD_OLD, FIELD_CURR, FIELD_CURL = 0, 1, 2
 PCG_NONE, PCG_MG, PCG_MG_TRI = 0, 1, 2
+NOALLOC_MAX_N = 1 << 28   # INK_NOALLOC_MAX_N
 
 
 class InkParams(C.Structure):
@@ -83,6 +84,7 @@ SYMBOLS = {
     "ink_get_stream": (_I, [_VP, C.POINTER(_VP)]),
     "ink_get_stats": (_I, [_VP, C.POINTER(InkStats)]),
     "ink_get_phase_ms": (_I, [_VP, C.POINTER(C.c_float)]),
+    "ink_check_finite_noalloc": (_I, [_VP, _VP, _VP, _L, _L, _I, _I, _VP, _VP]),
 }
 
 _lib = None

@@ -12,6 +12,7 @@
 #include <cstdlib>
 #include <chrono>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <utility>
 #include <vector>
@@ -1763,6 +1764,145 @@ struct Ctx final : CtxBase {
     }
 };
 
+// =================================================================================================
+// ink_check_finite_noalloc — the checkNanAndInf reduction for callers that cannot allocate device memory.
+//
+// Every other entry point needs an ink_ctx, and ink_create cudaMallocs the whole simulation state.  Two kinds of host cannot
+// go that way: (1) an application that reserved all of HBM for its own arena at start-up (a renderer, or a solver that already
+// holds the grid and the particles in its own buffers): cudaMalloc simply fails there; (2) a frame loop that must not stall:
+// cudaMalloc / cudaFree synchronise the whole device, so one call in the loop holds up every other stream of the process.
+// Such a host keeps the state in ITS buffers and only wants this library to look at them.  The kernel below is
+// k_check_finite (grid_kernels.cuh) with two changes: element t is read at x[t * stride] so that the AoS particle layout of
+// the ABI (N x 3) works as well as three dense arrays, and the two counters are not atomically added to a cudaMalloc'ed
+// accumulator: every block leaves its two partial counts in its own slot of the static array g_noalloc_scratch, and the block
+// that takes the last ticket adds the slots up in slot order and writes the caller's output.  That array is all the scratch
+// there is; its size bounds the number of blocks and with it the number of elements one call can cover (kNoAllocMaxN).
+//
+// The array lives in the module image: every GPU on which this library's kernels are loaded carries a copy of it until the
+// process exits.  On the HOST the name g_noalloc_scratch is only a handle for the runtime — handing `g_noalloc_scratch`
+// itself to a kernel would give it a host address — so the first call on each device (with that device current) asks the
+// runtime for that device's copy with cudaGetSymbolAddress and keeps the answer in g_noalloc_dev[device].
+// =================================================================================================
+constexpr int kNoAllocBlock = 256;                       // threads per block
+constexpr int kNoAllocPerThread = 32;                    // elements per thread: a block covers 8192 consecutive elements
+constexpr int kNoAllocMaxBlocks = 32768;                 // slots in the scratch array
+constexpr long long kNoAllocMaxN = (long long)kNoAllocMaxBlocks * kNoAllocBlock * kNoAllocPerThread;   // 2^28 elements per call
+constexpr size_t kNoAllocHeadBytes = 256;                // [0, 256): the block ticket (must be 0 when a launch starts)
+constexpr size_t kNoAllocScratchBytes = kNoAllocHeadBytes + (size_t)kNoAllocMaxBlocks * sizeof(uint2);   // 256 B + 256 KiB
+static_assert(kNoAllocMaxN == INK_NOALLOC_MAX_N, "include/ink_capi.h states the limit");
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];
+
+constexpr int kNoAllocMaxDevices = 64;
+static void* g_noalloc_dev[kNoAllocMaxDevices] = {};     // device address of g_noalloc_scratch on device d (0 = not asked yet)
+static std::mutex g_noalloc_mu;
+
+template <class Real>
+__global__ void __launch_bounds__(kNoAllocBlock) k_check_finite_noalloc(long long n, long long stride, const Real* __restrict__ x, const Real* __restrict__ y,
+                                                                         const Real* __restrict__ z, int check_norm, unsigned char* __restrict__ scratch,
+                                                                         unsigned long long* __restrict__ counts) {
+    unsigned int* ticket = reinterpret_cast<unsigned int*>(scratch);
+    uint2* slot = reinterpret_cast<uint2*>(scratch + kNoAllocHeadBytes);
+    __shared__ unsigned int s_bad[kNoAllocBlock / 32], s_big[kNoAllocBlock / 32];
+    __shared__ bool s_last;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    unsigned int bad = 0, big = 0;
+    const long long t0 = (long long)blockIdx.x * (kNoAllocBlock * kNoAllocPerThread) + threadIdx.x;
+#pragma unroll 4
+    for (int q = 0; q < kNoAllocPerThread; ++q) {
+        const long long t = t0 + (long long)q * kNoAllocBlock;
+        if (t < n) {
+            const Real a = x[t * stride], b = y[t * stride], c = z[t * stride];
+            if (!(isfinite(a) && isfinite(b) && isfinite(c))) ++bad;
+            if (check_norm && !(norm3(a, b, c) < Real(10000))) ++big;     // the same two tests as k_check_finite
+        }
+    }
+    bad = __reduce_add_sync(0xffffffffu, bad);
+    big = __reduce_add_sync(0xffffffffu, big);
+    if (lane == 0) { s_bad[wid] = bad; s_big[wid] = big; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned int tb = 0, tg = 0;
+        for (int q = 0; q < kNoAllocBlock / 32; ++q) { tb += s_bad[q]; tg += s_big[q]; }
+        slot[blockIdx.x] = make_uint2(tb, tg);            // a slot is always written before it is read: nothing of an earlier call survives
+        __threadfence();
+        s_last = (atomicAdd(ticket, 1u) == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    unsigned long long sb = 0, sg = 0;
+    for (unsigned int q = threadIdx.x; q < gridDim.x; q += kNoAllocBlock) {
+        const uint2 v = __ldcg(&slot[q]);
+        sb += v.x; sg += v.y;
+    }
+    __shared__ unsigned long long s_tot[2][kNoAllocBlock / 32];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { sb += __shfl_xor_sync(0xffffffffu, sb, o); sg += __shfl_xor_sync(0xffffffffu, sg, o); }
+    if (lane == 0) { s_tot[0][wid] = sb; s_tot[1][wid] = sg; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long ab = 0, ag = 0;
+        for (int q = 0; q < kNoAllocBlock / 32; ++q) { ab += s_tot[0][q]; ag += s_tot[1][q]; }
+        counts[0] = ab; counts[1] = ag;
+        *ticket = 0;                                       // leave the ticket as the next launch needs it
+    }
+}
+
+static int noalloc_fail(int rc, const char* what, cudaError_t e = cudaSuccess) {
+    char buf[512];
+    if (e != cudaSuccess) snprintf(buf, sizeof buf, "ink_check_finite_noalloc: %s -> %s", what, cudaGetErrorString(e));
+    else snprintf(buf, sizeof buf, "ink_check_finite_noalloc: %s", what);
+    g_create_error = buf;
+    return rc;
+}
+
+static int check_finite_noalloc(const void* x, const void* y, const void* z, int64_t n, int64_t stride, int dtype, int check_norm,
+                                uint64_t* counts_dev, void* cuda_stream) {
+    if (!counts_dev) return noalloc_fail(2, "counts_dev is NULL");
+    if (n < 0) return noalloc_fail(2, "n is negative");
+    if (n > kNoAllocMaxN) {
+        char buf[160];
+        snprintf(buf, sizeof buf, "n = %lld is beyond INK_NOALLOC_MAX_N = %lld elements per call (the static scratch array has one slot per 8192 elements): split the range",
+                 (long long)n, kNoAllocMaxN);
+        return noalloc_fail(2, buf);
+    }
+    if (n > 0 && (!x || !y || !z)) return noalloc_fail(2, "x, y or z is NULL");
+    if (stride < 1) return noalloc_fail(2, "stride must be >= 1 (1: three dense arrays, 3: one N x 3 array passed as p, p + 1, p + 2)");
+    if (dtype != 32 && dtype != 64) return noalloc_fail(2, "dtype must be 32 (float) or 64 (double)");
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) { cudaGetLastError(); return noalloc_fail(3, "cudaGetDevice (no CUDA device: there is no CPU path)", e); }
+    if (dev < 0 || dev >= kNoAllocMaxDevices) return noalloc_fail(3, "device ordinal beyond 63");
+    void* scratch;
+    {
+        // once per device, with that device current: where this device keeps its copy of g_noalloc_scratch
+        std::lock_guard<std::mutex> lk(g_noalloc_mu);
+        if (!g_noalloc_dev[dev]) {
+            void* p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+            if (e != cudaSuccess || !p) { cudaGetLastError(); return noalloc_fail(1, "cudaGetSymbolAddress(g_noalloc_scratch)", e); }
+            g_noalloc_dev[dev] = p;
+        }
+        scratch = g_noalloc_dev[dev];
+    }
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    // the ticket has to be 0 when the kernel starts; a launch that ran to its end left it so, this covers one that did not
+    e = cudaMemsetAsync(scratch, 0, kNoAllocHeadBytes, st);
+    if (e != cudaSuccess) return noalloc_fail(1, "cudaMemsetAsync(ticket)", e);
+    const unsigned int grid = (unsigned int)std::max<long long>(1, (n + kNoAllocBlock * kNoAllocPerThread - 1) / (kNoAllocBlock * kNoAllocPerThread));
+    unsigned long long* out = reinterpret_cast<unsigned long long*>(counts_dev);
+    if (dtype == 32)
+        k_check_finite_noalloc<float><<<grid, kNoAllocBlock, 0, st>>>((long long)n, (long long)stride, (const float*)x, (const float*)y, (const float*)z, check_norm,
+                                                                      (unsigned char*)scratch, out);
+    else
+        k_check_finite_noalloc<double><<<grid, kNoAllocBlock, 0, st>>>((long long)n, (long long)stride, (const double*)x, (const double*)y, (const double*)z, check_norm,
+                                                                       (unsigned char*)scratch, out);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return noalloc_fail(1, "kernel launch", e);
+    return 0;
+}
+
 }  // namespace ink
 
 // -------------------------------------------------------------------------------------------------
@@ -1864,5 +2004,9 @@ int ink_set_phantom(ink_ctx* c, int32_t have, const double v[3]) { return c->imp
 int ink_get_stream(ink_ctx* c, void** cuda_stream) { *cuda_stream = (void*)c->impl->stream; return 0; }
 int ink_get_stats(ink_ctx* c, ink_stats* out) { *out = c->impl->stats; return 0; }
 int ink_get_phase_ms(ink_ctx* c, float out[8]) { return c->impl->phase_ms(out); }
+int ink_check_finite_noalloc(const void* x, const void* y, const void* z, int64_t n, int64_t stride, int dtype, int check_norm, uint64_t* counts_dev,
+                             void* cuda_stream) {
+    return check_finite_noalloc(x, y, z, n, stride, dtype, check_norm, counts_dev, cuda_stream);
+}
 
 }  // extern "C"
