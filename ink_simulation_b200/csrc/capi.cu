@@ -56,6 +56,8 @@ static thread_local std::string g_create_error;
 
 // launch with the programmatic-stream-serialization attribute (see INK_PDL in common.cuh); INK_NO_PDL=1 disables it
 static const bool g_use_pdl = [] { const char* e = getenv("INK_NO_PDL"); return !(e && atoi(e) != 0); }();
+// INK_TEST_FAIL_CAPTURE=1 (tests only): behave as if the runtime refused cudaStreamBeginCapture, to exercise the fallback below
+static const bool g_fail_capture = [] { const char* e = getenv("INK_TEST_FAIL_CAPTURE"); return e && atoi(e) != 0; }();
 template <class... KArgs, class... Args>
 static inline void launch_k(void (*kern)(KArgs...), unsigned int grid, unsigned int block, size_t smem, cudaStream_t st, Args&&... args) {
     cudaLaunchConfig_t cfg = {};
@@ -84,6 +86,13 @@ static inline void launch_cluster(void (*kern)(KArgs...), unsigned int ctas, uns
         launch_k(kern, (grid), (block), 0, stream, __VA_ARGS__);         \
         ++stats.kernel_launches;                                         \
     } while (0)
+
+// frees a temporary device allocation on every way out of a function (the CK macro returns early on error)
+struct DevTmp {
+    void* p = nullptr;
+    ~DevTmp() { if (p) cudaFree(p); }
+    template <class T> T* as() const { return static_cast<T*>(p); }
+};
 
 static inline unsigned int nblk(long long n, int b = 256) { return (unsigned int)((n + b - 1) / b); }
 
@@ -687,11 +696,12 @@ struct Ctx final : CtxBase {
         const long long n = (long long)nr * ni * nj;
         const long long first = n * rank / world, count = n * (rank + 1) / world - first;
         const size_t ntab = (size_t)nr + 2 * (size_t)ni + 2 * (size_t)nj;
-        float* tab = nullptr;
-        Real *dpos = nullptr, *dvel = nullptr;
-        CK(cudaMalloc(&tab, ntab * sizeof(float)));
-        CK(cudaMalloc(&dpos, (size_t)std::max<long long>(count, 1) * 3 * sizeof(Real)));
-        CK(cudaMalloc(&dvel, (size_t)std::max<long long>(count, 1) * 3 * sizeof(Real)));
+        DevTmp t_tab, t_pos, t_vel;   // freed on every return, the early error returns of CK included
+        CK(cudaMalloc(&t_tab.p, ntab * sizeof(float)));
+        CK(cudaMalloc(&t_pos.p, (size_t)std::max<long long>(count, 1) * 3 * sizeof(Real)));
+        CK(cudaMalloc(&t_vel.p, (size_t)std::max<long long>(count, 1) * 3 * sizeof(Real)));
+        float* tab = t_tab.as<float>();
+        Real *dpos = t_pos.as<Real>(), *dvel = t_vel.as<Real>();
         float *tr = tab, *tsi = tr + nr, *tci = tsi + ni, *tsj = tci + ni, *tcj = tsj + nj;
         CK(cudaMemcpyAsync(tr, radius, nr * sizeof(float), cudaMemcpyHostToDevice, stream));
         CK(cudaMemcpyAsync(tsi, si, ni * sizeof(float), cudaMemcpyHostToDevice, stream));
@@ -704,18 +714,17 @@ struct Ctx final : CtxBase {
                    (const float*)tcj, c, P.X / 2.f, P.Y - 0.1f, P.Z / 2.f, dpos, dvel);
         CK(cudaGetLastError());
         CK(cudaStreamSynchronize(stream));
-        const int rc = set_particles_shard(drop, dpos, dvel, count, (int)sizeof(Real) * 8);
-        cudaFree(tab); cudaFree(dpos); cudaFree(dvel);
-        return rc;
+        return set_particles_shard(drop, dpos, dvel, count, (int)sizeof(Real) * 8);
     }
     int seed_box(int drop, const int32_t* rnd, int64_t n) override {
         if (n < 0) { err = "seed_box: bad n"; return 2; }
         const long long first = (long long)n * rank / world, count = (long long)n * (rank + 1) / world - first;
-        int32_t* drnd = nullptr;
-        Real *dpos = nullptr, *dvel = nullptr;
-        CK(cudaMalloc(&drnd, (size_t)std::max<long long>(count, 1) * 3 * sizeof(int32_t)));
-        CK(cudaMalloc(&dpos, (size_t)std::max<long long>(count, 1) * 3 * sizeof(Real)));
-        CK(cudaMalloc(&dvel, (size_t)std::max<long long>(count, 1) * 3 * sizeof(Real)));
+        DevTmp t_rnd, t_pos, t_vel;
+        CK(cudaMalloc(&t_rnd.p, (size_t)std::max<long long>(count, 1) * 3 * sizeof(int32_t)));
+        CK(cudaMalloc(&t_pos.p, (size_t)std::max<long long>(count, 1) * 3 * sizeof(Real)));
+        CK(cudaMalloc(&t_vel.p, (size_t)std::max<long long>(count, 1) * 3 * sizeof(Real)));
+        int32_t* drnd = t_rnd.as<int32_t>();
+        Real *dpos = t_pos.as<Real>(), *dvel = t_vel.as<Real>();
         if (count > 0) {
             CK(cudaMemcpyAsync(drnd, rnd + 3 * first, (size_t)count * 3 * sizeof(int32_t), cudaMemcpyHostToDevice, stream));
             // bounds exactly as the reference writes them: float expressions for x and z, double literals for y (src/system.cpp:102-104)
@@ -724,9 +733,7 @@ struct Ctx final : CtxBase {
         }
         CK(cudaGetLastError());
         CK(cudaStreamSynchronize(stream));
-        const int rc = set_particles_shard(drop, dpos, dvel, count, (int)sizeof(Real) * 8);
-        cudaFree(drnd); cudaFree(dpos); cudaFree(dvel);
-        return rc;
+        return set_particles_shard(drop, dpos, dvel, count, (int)sizeof(Real) * 8);
     }
     int num_drops() const override { return (int)drop_n.size(); }
     int64_t num_particles(int drop) const override { return (drop >= 0 && drop < (int)drop_n.size()) ? drop_n[drop] : 0; }
@@ -1448,8 +1455,20 @@ struct Ctx final : CtxBase {
     }
     // capture `body(dc)` once per parity into a graph (thread-local capture mode: other host threads of the process are not
     // affected), then replay it.  The cached pair belongs to one solution vector x; another x recaptures.
+    // A capture or an instantiation the runtime refuses (a driver without programmatic-dependency edges in captures, another
+    // capture open on this thread, ...) is not an error of the solve: the ctx drops to plain launches for good (use_graph = false,
+    // one line under INK_VERBOSE) and runs the iteration directly.  Only what the body itself returns is a hard failure.
+    template <class Body>
+    int graph_fallback(int dc, Body& body, const char* what, cudaError_t e) {
+        cudaGetLastError();   // clear the sticky-free error state the failed call left
+        use_graph = false;
+        for (auto& ge : it_graph) if (ge) { cudaGraphExecDestroy(ge); ge = nullptr; }
+        if (getenv("INK_VERBOSE")) fprintf(stderr, "[inkb200] %s failed (%s): PCG iterations run as plain launches from here on\n", what, cudaGetErrorString(e));
+        return body(dc);
+    }
     template <class Body>
     int replay_iteration(int dc, const void* x, Body& body) {
+        if (!use_graph) return body(dc);   // fell back earlier in this solve
         if (it_graph_x != x) {
             for (auto& ge : it_graph) if (ge) { cudaGraphExecDestroy(ge); ge = nullptr; }
             it_graph_x = x;
@@ -1457,16 +1476,18 @@ struct Ctx final : CtxBase {
         if (!it_graph[dc]) {
             const long long before = stats.kernel_launches;
             cudaGraph_t gr = nullptr;
-            CK(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
+            const cudaError_t be = g_fail_capture ? cudaErrorStreamCaptureUnsupported : cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal);
+            if (be != cudaSuccess) return graph_fallback(dc, body, "cudaStreamBeginCapture", be);
             const int rc = body(dc);
             const cudaError_t ce = cudaStreamEndCapture(stream, &gr);
-            if (rc) { if (gr) cudaGraphDestroy(gr); return rc; }
-            if (ce != cudaSuccess) { err = std::string("graph capture of the PCG iteration failed: ") + cudaGetErrorString(ce); return 1; }
-            it_graph_nodes = stats.kernel_launches - before;
+            const long long nodes = stats.kernel_launches - before;
             stats.kernel_launches = before;   // capturing launched nothing
+            if (rc) { if (gr) cudaGraphDestroy(gr); cudaGetLastError(); return rc; }
+            if (ce != cudaSuccess || !gr) return graph_fallback(dc, body, "graph capture of the PCG iteration", ce);
             const cudaError_t ie = cudaGraphInstantiate(&it_graph[dc], gr, 0);
             cudaGraphDestroy(gr);
-            if (ie != cudaSuccess) { it_graph[dc] = nullptr; err = std::string("cudaGraphInstantiate failed: ") + cudaGetErrorString(ie); return 1; }
+            if (ie != cudaSuccess) { it_graph[dc] = nullptr; return graph_fallback(dc, body, "cudaGraphInstantiate", ie); }
+            it_graph_nodes = nodes;
         }
         CK(cudaGraphLaunch(it_graph[dc], stream));
         stats.kernel_launches += it_graph_nodes;

@@ -88,7 +88,7 @@ __global__ void __launch_bounds__(256) k_particles_rk2(Grid g, Consts<Real> C, R
 // ------------------------------------------------------------------------------------------------
 constexpr int kTileThreads = 256;
 constexpr int kTileKP = 4;                       // particles per thread at most (chunk <= 1024 slots)
-constexpr int kTileSmemBytes = 56 * 1024;        // 4 blocks per SM
+constexpr int kTileSmemBytes = 56 * 1024;        // 3 blocks per SM: 3 x (56 KB + 1 KB reserved + the static mbarrier / reduction arrays) fits the 228 KB carve-out, 4 x does not
 
 // one block per half-row r = 2j + hy: split its slot range into equal chunks of at most `chunk` slots
 __global__ void __launch_bounds__(128) k_tile_worklist(int X, int Y, int Z, long long np, const uint32_t* __restrict__ bin_off, int chunk,
@@ -155,7 +155,7 @@ __device__ __forceinline__ bool get_velocity3_tile(const Real* tile, const TileG
 }
 
 template <class Real, bool FAST>
-__global__ void __launch_bounds__(kTileThreads, 4) k_particles_rk2_tile(Grid g, Consts<Real> C, Real dt, Particles<Real> P,
+__global__ void __launch_bounds__(kTileThreads, 3) k_particles_rk2_tile(Grid g, Consts<Real> C, Real dt, Particles<Real> P,
                                                                          const Real* __restrict__ u, const Real* __restrict__ v, const Real* __restrict__ w,
                                                                          uint8_t* __restrict__ seed, const uint2* __restrict__ work,
                                                                          const unsigned int* __restrict__ nwork) {

@@ -3,6 +3,7 @@
 
 #include <cmath>
 #include <cstdlib>
+#include <cstring>
 #include <fstream>
 #include <sstream>
 #include <stdexcept>
@@ -112,6 +113,8 @@ extern "C" long inkhost_emitter_scene(int X, int Y, int Z, float* pos, float* ve
 
 // one drop of n particles in the initParticles box, drawn the way a fresh process draws them: glibc rand() is never seeded
 // by the reference, i.e. the sequence of srand(1)
+// SIDE EFFECT: re-seeds the process-global rand() (inkseed::box draws from rand() like the reference's initParticles does); a
+// caller that uses rand() itself should take inkhost_rand_stream + ink_seed_box instead, which leave the global generator alone.
 extern "C" long inkhost_box_scene(int X, int Y, int Z, int n, float* pos, long cap) {
     std::srand(1);
     std::vector<std::vector<Particle>> drops;
@@ -142,7 +145,13 @@ extern "C" void inkhost_emitter_tables(float* radius, int* nr, float* sin_i, flo
     for (int a = 0; a < *ni && a < cap; ++a) { sin_i[a] = si[a]; cos_i[a] = ci[a]; }
     for (int a = 0; a < *nj && a < cap; ++a) { sin_j[a] = sj[a]; cos_j[a] = cj[a]; }
 }
-extern "C" void inkhost_rand_stream(int32_t* out, long n) {   // a fresh process's rand() sequence (the reference never seeds it)
-    std::srand(1);
-    for (long a = 0; a < n; ++a) out[a] = rand();
+// a fresh process's rand() sequence (the reference never seeds it).  glibc's rand() is random() on the default 128-byte TYPE_3
+// state; the same generator on a PRIVATE state (initstate_r with seed 1) gives the same numbers without re-seeding the
+// process-global one under the caller's feet (tests/test_host_cpp.py compares both).
+extern "C" void inkhost_rand_stream(int32_t* out, long n) {
+    char statebuf[128];
+    struct random_data rd;
+    memset(&rd, 0, sizeof rd);
+    initstate_r(1u, statebuf, sizeof statebuf, &rd);
+    for (long a = 0; a < n; ++a) { int32_t v; random_r(&rd, &v); out[a] = v; }
 }

@@ -545,3 +545,35 @@ def test_gpu_every_kernel_variant_runs_on_ragged_grids():
 
     out = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "sanitize_r2.py")], capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and "sanitize_r2: done" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
+
+
+def test_gpu_refused_graph_capture_falls_back_to_plain_launches():
+    """a runtime that refuses the capture of the PCG iteration (simulated by INK_TEST_FAIL_CAPTURE=1) must not fail
+    ink_step: the ctx drops to plain launches (graph_launches stays 0, one INK_VERBOSE line) and, the kernels and their order
+    being the same, produces the same bits as the graph path.  Own processes: the switch is read when the library loads."""
+    import subprocess
+    import sys
+
+    code = (
+        "import sys, hashlib, numpy as np\n"
+        f"sys.path.insert(0, {ROOT!r}); sys.path.insert(0, {os.path.join(ROOT, 'tests')!r})\n"
+        "import util\n"
+        "from ink_simulation_b200 import System\n"
+        "dims = util.C2\n"
+        "S = System(*dims, cg_rtol=1e-7)\n"
+        "S.set_velocity(*util.rand_field(dims, 71, scale=0.5)); S.set_particles(util.box_particles(dims, 20000, 72))\n"
+        "for _ in range(3): S.solve(0.35)\n"
+        "st = S.stats()\n"
+        "h = hashlib.sha1(np.stack(S.get_velocity()).tobytes() + S.get_particles()[0].tobytes()).hexdigest()\n"
+        "print('RESULT', h, st.cg_iters, st.graph_launches)\n"
+    )
+    res = {}
+    for fail in ("0", "1"):
+        env = dict(os.environ, INK_TEST_FAIL_CAPTURE=fail, INK_VERBOSE="1")
+        out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300, env=env)
+        assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
+        line = [l for l in out.stdout.splitlines() if l.startswith("RESULT")][0].split()
+        res[fail] = (line[1], int(line[2]), int(line[3]), out.stderr)
+    assert res["0"][2] > 0 and res["1"][2] == 0
+    assert "plain launches" in res["1"][3] and "plain launches" not in res["0"][3]
+    assert res["0"][:2] == res["1"][:2]

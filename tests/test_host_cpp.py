@@ -100,6 +100,26 @@ def glibc_box_particles(dims, n):
     return out
 
 
+def test_rand_stream_is_the_unseeded_rand_sequence_and_leaves_the_global_generator_alone():
+    """inkhost_rand_stream used to call srand(1) on the process-global generator.  It now draws from a private
+    random_r state: same numbers as a fresh process's rand() (what the reference's initParticles consumes), and a
+    caller's own rand() sequence is not disturbed by it."""
+    import ctypes
+
+    from ink_simulation_b200 import seeding
+
+    libc = ctypes.CDLL(None)
+    libc.srand(1)
+    want = np.array([libc.rand() for _ in range(1000)], dtype=np.int32)
+    assert np.array_equal(seeding.rand_stream(1000), want)
+    libc.srand(7)
+    a = [libc.rand() for _ in range(5)]
+    libc.srand(7)
+    first = libc.rand()
+    seeding.rand_stream(100)
+    assert [first] + [libc.rand() for _ in range(4)] == a
+
+
 @pytest.mark.gpu
 def test_inksim_binary_end_to_end(tmp_path):
     from ink_simulation_b200 import System
