@@ -656,17 +656,17 @@ def main():
                                       "note": "20 launches with dt = 0 right after a re-binning (cache-warm field)"}
         # CG iteration pair ALONE (k_cg_dir_matvec + k_cg_update), no preconditioner: 10*R B/cell/iteration; exactly 100
         # iterations (cg_max_iters = 100, tolerance 1e-30 on a random right-hand side is never met)
-        import ctypes as C
+        from ink_simulation_b200.system import _ptr
 
         S2 = System(*dims, dtype=dtype, device=local, cg_rtol=1e-30 if rbytes == 8 else 0.0, cg_max_iters=100, cg_check_every=100, cg_precond="none")
         b = torch.randn(dims, dtype=torch.float32 if rbytes == 4 else torch.float64, device="cuda")
         pout = torch.empty_like(b)
         torch.cuda.synchronize()
         hd = 32 if rbytes == 4 else 64
-        S2._ck(S2.L.ink_poisson_solve(S2.h, C.c_void_p(b.data_ptr()), C.c_void_p(pout.data_ptr()), hd))
+        S2._ck(S2.L.ink_poisson_solve(S2.h, _ptr(b), _ptr(pout), hd))   # _ptr orders the device inputs before the ctx stream
         ext2, f0, f1 = H.events(S2)
         f0.record(ext2)
-        S2._ck(S2.L.ink_poisson_solve(S2.h, C.c_void_p(b.data_ptr()), C.c_void_p(pout.data_ptr()), hd))
+        S2._ck(S2.L.ink_poisson_solve(S2.h, _ptr(b), _ptr(pout), hd))   # _ptr orders the device inputs before the ctx stream
         f1.record(ext2)
         f1.synchronize()
         ms = f0.elapsed_time(f1)

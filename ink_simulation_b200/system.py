@@ -36,17 +36,49 @@ class InkError(RuntimeError):
 
 
 def _ptr(a):
+    """Pointer of `a` for the C ABI, with the ordering the ABI asks for: the ctx runs on its own non-blocking stream, so a DEVICE
+    input must be complete before the call (include/ink_capi.h).  numpy arrays and host tensors need nothing.  A torch CUDA tensor:
+    torch's current stream of its device is synchronised.  Any other object with __cuda_array_interface__ (cupy, numba, ...): the
+    stream the interface names is synchronised (v3 `stream`: 1 = legacy default, 2 = per-thread default, else a cudaStream_t), the
+    whole device when it names none.  A bare integer address carries no such information: the caller orders it (synchronise, or
+    make the ctx stream from cuda_stream() wait on an event)."""
     if a is None:
         return None
     if isinstance(a, np.ndarray):
         return a.ctypes.data_as(C.c_void_p)
     if hasattr(a, "data_ptr"):  # torch tensor (host pinned or device) — plumbing only
-        if getattr(a, "is_cuda", False):   # the ctx runs on its own non-blocking stream: device inputs must be complete (ink_capi.h)
+        if getattr(a, "is_cuda", False):
             import torch
 
             torch.cuda.current_stream(a.device).synchronize()
         return C.c_void_p(a.data_ptr())
+    cai = getattr(a, "__cuda_array_interface__", None)
+    if cai is not None:
+        import torch
+
+        st = cai.get("stream")
+        if st is None:
+            torch.cuda.synchronize()
+        elif st == 1:
+            torch.cuda.default_stream().synchronize()     # torch's default stream is the legacy default stream
+        elif st == 2:
+            torch.cuda.synchronize()                      # per-thread default stream: no handle to wait on, take the device
+        else:
+            torch.cuda.ExternalStream(int(st)).synchronize()
+        return C.c_void_p(int(cai["data"][0]))
     return C.c_void_p(int(a))
+
+
+def _dev_meta(a):
+    """(shape, itemsize, contiguous) of a torch tensor or of any __cuda_array_interface__ object"""
+    if hasattr(a, "data_ptr"):
+        return tuple(a.shape), a.element_size(), a.is_contiguous()
+    cai = a.__cuda_array_interface__
+    return tuple(cai["shape"]), np.dtype(cai["typestr"]).itemsize, cai.get("strides") is None
+
+
+def _is_dev_like(a):
+    return hasattr(a, "data_ptr") or hasattr(a, "__cuda_array_interface__")
 
 
 def nccl_unique_id() -> bytes:
@@ -236,10 +268,10 @@ class System:
 
     # ---- state
     def set_particles(self, pos, vel=None, drop=0):
-        if hasattr(pos, "data_ptr"):  # torch tensor: float32/float64, contiguous (N,3)
-            n = pos.shape[0]
-            hd = 32 if pos.element_size() == 4 else 64
-            self._ck(self.L.ink_set_particles(self.h, drop, _ptr(pos), _ptr(vel), n, hd))
+        if _is_dev_like(pos):  # torch tensor or __cuda_array_interface__ object: float32/float64, contiguous (N,3)
+            shape, isz, contig = _dev_meta(pos)
+            assert len(shape) == 2 and shape[1] == 3 and contig
+            self._ck(self.L.ink_set_particles(self.h, drop, _ptr(pos), _ptr(vel), shape[0], 32 if isz == 4 else 64))
             return
         pos = self._a(pos).reshape(-1, 3)
         v = None if vel is None else self._a(vel).reshape(-1, 3)
@@ -274,10 +306,10 @@ class System:
         return pos, vel
 
     def set_velocity(self, u, v, w):
-        if hasattr(u, "data_ptr"):   # torch tensors (host or DEVICE), contiguous, (X, Y, Z): pointers go straight to the C ABI
-            assert tuple(u.shape) == self.dims and tuple(v.shape) == self.dims and tuple(w.shape) == self.dims
-            assert u.is_contiguous() and v.is_contiguous() and w.is_contiguous()
-            self._ck(self.L.ink_set_velocity(self.h, _ptr(u), _ptr(v), _ptr(w), 32 if u.element_size() == 4 else 64))
+        if _is_dev_like(u):   # torch tensors (host or DEVICE) or __cuda_array_interface__ objects, contiguous, (X, Y, Z): pointers go straight to the C ABI
+            metas = [_dev_meta(a) for a in (u, v, w)]
+            assert all(m[0] == self.dims and m[2] for m in metas) and len({m[1] for m in metas}) == 1
+            self._ck(self.L.ink_set_velocity(self.h, _ptr(u), _ptr(v), _ptr(w), 32 if metas[0][1] == 4 else 64))
             return
         u, v, w = self._a(u), self._a(v), self._a(w)
         assert u.shape == self.dims and v.shape == self.dims and w.shape == self.dims
