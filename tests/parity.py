@@ -20,12 +20,16 @@ GOLDEN = sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)
 P_TOL = 2e-5
 VEL_TOL = 1e-5
 POS_TOL = 1e-6
-# END-OF-STEP velocity (after vorticity confinement) per fixture.  The north_star's 1e-5 is on the PROJECTED field
-# (check_pressure).  The confinement force N x omega with N = grad|omega| / |omega| is not normalised and amplifies
-# the pressure round-off where |omega| is small; at 20x45x20 the reference's own fp32 SparseLU is 6.0e-6 (p) / 3.4e-6
-# (projected velocity) away from the exact solution, which the rough random injected field turns into 2.1e-5 at the end of
-# step 0 (3e-6 on the developed fields of steps 1-2) — measured with the fp64 DST oracle, i.e. it is the reference's noise.
-STEP_VEL_TOL = {(20, 45, 20): 5e-5}
+# END-OF-STEP velocity (after vorticity confinement).  The north_star's 1e-5 is on the PROJECTED field (check_pressure) and holds
+# everywhere.  At the end of a step it holds too, with ONE exception: step 0 of the 20x45x20 fixture.  The confinement force
+# N x omega with N = grad|omega| / |omega| is not normalised and amplifies pressure round-off where |omega| is small;
+# the reference's own fp32 SparseLU is 6.0e-6 (p) / 3.4e-6 (projected velocity) away from the exact solution there, which the rough
+# random injected field turns into 2.09e-5 at the end of step 0 (3.0e-6 / 2.0e-6 on the developed fields of steps 1-2).  That
+# number is the REFERENCE's noise: it is what the oracle with the exact fp64 DST solve measures against the fixture
+# (MEASURED_STEP_VEL, asserted to within 10 % by the oracle test so that drift shows), and check_solve's `exact` argument holds the
+# implementation under test to 1e-5 against that exact-solve oracle on the very same step.
+STEP_VEL_TOL = {((20, 45, 20), 0): 3e-5}
+MEASURED_STEP_VEL = {((20, 45, 20), 0): 2.09e-5}     # oracle (exact solve) vs compiled reference, tests/test_oracle_golden.py
 
 
 def load(path):
@@ -94,26 +98,38 @@ def check_pressure(make, G, p_tol=P_TOL, vel_tol=VEL_TOL):
     return ep, ev
 
 
-def check_solve(make, G, vel_tol=None, pos_tol=POS_TOL):
+def check_solve(make, G, vel_tol=None, pos_tol=POS_TOL, exact=None):
     """Three System::solve steps.  Step 0 starts from identical state; later steps are re-synchronised to the
-    reference's state first (parity is judged per step from identical input)."""
+    reference's state first (parity is judged per step from identical input).
+    exact: optional factory of the oracle with the exact pressure solve; the same step must then ALSO agree with it at VEL_TOL /
+    pos_tol, so that a loosened STEP_VEL_TOL entry only ever covers the reference's own solver noise."""
     dims = tuple(int(x) for x in G["dims"])
-    if vel_tol is None:
-        vel_tol = STEP_VEL_TOL.get(dims, VEL_TOL)
     errs = []
     for s in range(3):
-        S = make(dims)
-        if s == 0:
-            S.set_velocity(G["u"], G["v"], G["w"]); S.set_particles(G["part"])
-        else:
-            S.set_velocity(*G[f"solve{s-1}_vel"]); S.set_particles(G[f"solve{s-1}_pos"])
+        tol = vel_tol if vel_tol is not None else STEP_VEL_TOL.get((dims, s), VEL_TOL)
+        todo = [make(dims)] + ([exact(dims)] if exact is not None else [])
+        for S in todo:
+            if s == 0:
+                S.set_velocity(G["u"], G["v"], G["w"]); S.set_particles(G["part"])
+            else:
+                S.set_velocity(*G[f"solve{s-1}_vel"]); S.set_particles(G[f"solve{s-1}_pos"])
+        S = todo[0]
         dt = S.solve(0.35)
         assert dt == float(G[f"solve{s}_dt"]), (s, dt, float(G[f"solve{s}_dt"]))
-        ev = rel_inf(np.stack(S.get_velocity()), G[f"solve{s}_vel"])
+        vel = np.stack(S.get_velocity())
+        ev = rel_inf(vel, G[f"solve{s}_vel"])
         pos = S.get_particles()[0]
         ref = G[f"solve{s}_pos"]
         ep = float(np.max(np.abs(pos.astype(np.float64) - ref) / np.maximum(np.abs(ref), 1.0)))
-        assert ev <= vel_tol, f"step {s}: velocity rel err {ev}"
+        assert ev <= tol, f"step {s}: velocity rel err {ev}"
         assert ep <= pos_tol, f"step {s}: particle rel err {ep}"
+        if exact is not None:
+            E = todo[1]
+            assert E.solve(0.35) == dt
+            ex = rel_inf(vel, np.stack(E.get_velocity()))
+            epos = E.get_particles()[0]
+            exp = float(np.max(np.abs(pos.astype(np.float64) - epos) / np.maximum(np.abs(epos), 1.0)))
+            assert ex <= VEL_TOL, f"step {s}: velocity rel err {ex} against the exact-solve oracle"
+            assert exp <= pos_tol, f"step {s}: particle rel err {exp} against the exact-solve oracle"
         errs.append((ev, ep))
     return errs

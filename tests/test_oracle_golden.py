@@ -19,7 +19,13 @@ def test_oracle_pressure_and_solve_vs_golden(oracle_mod, path):
     G = parity.load(path)
     mk = lambda d: oracle_mod.OracleSystem(*d, dtype=np.float32)  # noqa: E731
     parity.check_pressure(mk, G)
-    parity.check_solve(mk, G)
+    errs = parity.check_solve(mk, G)
+    # the one loosened end-of-step bound covers the reference's own SparseLU noise, measured here by the exact-solve oracle:
+    # keep the measurement in the test so that drift (of the oracle, or of a regenerated fixture) shows
+    dims = tuple(int(x) for x in G["dims"])
+    for (d, step), measured in parity.MEASURED_STEP_VEL.items():
+        if d == dims:
+            assert abs(errs[step][0] - measured) <= 0.1 * measured, (errs[step][0], measured)
 
 
 def test_oracle_fp64_close_to_fp32_reference(oracle_mod):
