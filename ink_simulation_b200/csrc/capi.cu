@@ -23,7 +23,6 @@
 #include "mg.cuh"
 #include "mg_vec.cuh"
 #include "mg_tri.cuh"
-#include "p2p.cuh"
 #include "grid_vec.cuh"
 #include "nccl_shim.h"
 #include "particle_kernels.cuh"
@@ -196,7 +195,7 @@ struct Ctx final : CtxBase {
     const void* it_graph_x = nullptr;     // the solution vector the cached graphs were captured for
     long long it_graph_nodes = 0;
     bool use_graph = true;
-    // multi-GPU: per-iteration exchanges by peer stores over NVLink (p2p.cuh) instead of NCCL calls
+    // multi-GPU: per-iteration exchanges by peer stores over NVLink (protocol: cg.cuh) instead of NCCL calls
     bool p2p = false;
     // INK_TRACE_ITER=k: CUDA-event timeline of CG iteration k of every solve, printed by rank 0 (diagnostic)
     int trace_iter = -1; bool tracing = false; bool host_timing = false;
@@ -389,7 +388,7 @@ struct Ctx final : CtxBase {
         return 0;
     }
 
-    // ---- peer-memory exchanges (p2p.cuh) ------------------------------------------------------------
+    // ---- peer-memory exchanges (cg.cuh) -------------------------------------------------------------
     // One arena per rank (mailboxes, flags, boundary-band payloads), exported over CUDA IPC; the handles travel once through
     // ncclAllGather.  Any failure (no peer access, odd row size, INK_NO_P2P=1) leaves p2p == false: the NCCL path is kept.
     int p2p_setup() {

@@ -29,6 +29,23 @@ struct CgScal {
     double partial[2][kCgMaxBlocks];
 };
 
+// ---- peer-memory exchanges (multi-GPU) -------------------------------------------------------------------------------------
+// Device-initiated exchanges over NVLink peer memory carry the per-iteration traffic of the distributed PCG (one process per
+// GPU; SURVEY 8e: y-slabs, 2 scalar all-reduces + 2 boundary-band exchanges per CG iteration).
+// Why not NCCL here: each of those messages is 8 bytes .. 1 MB and there are ~5 per iteration; an NCCL call costs 15-25 us of
+// launch + protocol latency regardless of size, i.e. ~110 us per iteration on top of ~120 us of compute (2 GPUs, profiles/r1_c).
+// Every rank instead owns one ARENA (a single cudaMalloc, exported with cudaIpcGetMemHandle and opened by the peers once at
+// start-up): peers store straight into it through NVLink and publish a sequence number; the consumer kernel spins on its LOCAL
+// flag.  NCCL stays for start-up (handle all-gather) and the large once-per-step collectives (velocity all-gather, force-mask
+// all-reduce), where it is at bandwidth.
+// Memory-ordering contract: producer = plain stores of the payload, __threadfence_system(), then a volatile store of the
+// sequence number; consumer = volatile load of the sequence number until it matches, __threadfence_system(), then the payload.
+// Payload consumers in LATER kernels see it through L2 (a kernel boundary orders them after the waiting kernel).
+// Boundary bands have no stand-alone put / wait kernels: the PRODUCER of a band stores it a second time into the neighbour's
+// arena and its last block publishes the sequence number (P2pPush below: k_cg_init / k_cg_update for r; k_band_restore_weight in
+// mg_vec.cuh for the weighted z), and the CONSUMER kernel spins on its local flag before it reads the arena (k_band_scale,
+// k_band_combine).  The separate put + wait-unpack kernel pair of the first version cost two launches per exchange on the
+// critical path (2 GPUs: 3.64 -> 2.99 ms per step when they were fused away).
 constexpr int kP2pMaxRanks = 16;
 
 struct alignas(64) P2pMail {
@@ -134,7 +151,7 @@ INK_HD Pack<Real, V> ldp(const Real* p) { return *reinterpret_cast<const Pack<Re
 template <class Real, int V>
 INK_HD void stp(Real* p, const Pack<Real, V>& v) { *reinterpret_cast<Pack<Real, V>*>(p) = v; }
 
-// Multi-GPU: a kernel that produces boundary rows can PUSH them straight into the neighbours' arenas (p2p.cuh) while it
+// Multi-GPU: a kernel that produces boundary rows can PUSH them straight into the neighbours' arenas (see the note above P2pMail) while it
 // writes them locally, and its last block publishes the sequence number: no separate put kernel on the critical path.
 // Cell offsets are relative to the first cell of this rank's slab; [0, lo_cells) goes to rank-1, [hi_start, ...) to rank+1.
 struct P2pPush {

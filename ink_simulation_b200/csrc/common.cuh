@@ -76,7 +76,7 @@ __device__ __forceinline__ float warp_max(float v) {
 
 constexpr int kSMs = 148;  // B200
 
-// spin until a sequence number published by a PEER GPU (p2p.cuh) has reached `want`; then order the payload reads after it
+// spin until a sequence number published by a PEER GPU (protocol: cg.cuh) has reached `want`; then order the payload reads after it
 __device__ __forceinline__ void p2p_spin(const volatile unsigned long long* flag, unsigned long long want) {
     while (*flag < want) {
 #if defined(__CUDA_ARCH__) && __CUDA_ARCH__ >= 700
