@@ -392,6 +392,68 @@ def rel_inf(a, b):
     return float(np.max(np.abs(a - b)) / max(np.max(np.abs(b)), 1e-300))
 
 
+def full_size_parity(dims, u, v, w, pos, vel, device=0, label=""):
+    """GPU path against the CPU oracle at FULL workload size, from one identical state (u, v, w, pos, vel), ONE step taken phase
+    by phase as tests/test_gpu_parity.py::test_gpu_step_phase_by_phase does at config 1: dt equal; convection, forces, viscosity
+    bit-exact; projected velocity <= 1e-5 of the field scale with a divergence no worse than the exact solve's; then, from the
+    oracle's projected field, vorticity and particles (positions AND velocities) bit-exact in strict arithmetic, and the
+    fast-arithmetic particle kernel <= 1e-6 relative apart from wall-clamp flips (counted).  The oracle is the checker here
+    (cpu_baseline leg / tests only); nothing timed runs through it."""
+    import oracle
+    from ink_simulation_b200 import System
+
+    oracle.build()
+    oracle.set_threads()
+    S = System(*dims, device=device, arith="strict", cg_rtol=1e-7)
+    O = oracle.OracleSystem(*dims, dtype=np.float32)
+    for T in (S, O):
+        T.set_velocity(u, v, w)
+        T.set_particles(pos, vel)
+    vstack = lambda T: np.stack(T.get_velocity())   # noqa: E731
+    dt = O.calc_dt(RENDER_DT)
+    out = {"case": f"{label}{dims[0]}x{dims[1]}x{dims[2]}, {len(pos)} particles, strict arithmetic, cg_rtol 1e-7, one step phase by phase "
+                   "from the developed state", "dt": dt, "dt_equal": bool(S.calc_dt(RENDER_DT) == dt)}
+    exact = {}
+    for ph in ("advect", "forces", "viscosity"):
+        getattr(O, ph)(dt); getattr(S, ph)(dt)
+        exact[ph] = bool(np.array_equal(vstack(O), vstack(S)))
+    O.pressure(dt); S.pressure(dt)
+    vo = vstack(O)
+    out["projected_vel_rel"] = rel_inf(vstack(S), vo)
+    out["p_rel"] = rel_inf(S.get_pressure(), O.get_pressure())
+    ds, do = float(np.abs(S.divergence()).max()), float(np.abs(O.divergence()).max())
+    out["div_max_gpu"], out["div_max_oracle"] = ds, do
+    out["div_ok"] = bool(ds <= do * 1.001 + 1e-5 * float(np.abs(vo).max()))
+    out["cg_iters"] = int(S.stats().cg_iters)
+    S.set_velocity(*O.get_velocity())             # identical input for the phases after the solve
+    O.vorticity(dt); S.vorticity(dt)
+    exact["vorticity"] = bool(np.array_equal(vstack(O), vstack(S)))
+    field = O.get_velocity()
+    pos0, vel0 = O.get_particles()
+    O.particles(dt); S.particles(dt)
+    po, vo_p = O.get_particles()
+    ps, vs_p = S.get_particles()
+    exact["particles"] = bool(np.array_equal(po, ps) and np.array_equal(vo_p, vs_p))
+    out["pos_rel"] = float(np.max(np.abs(ps.astype(np.float64) - po) / np.maximum(np.abs(po), 1.0)))
+    S.close()
+    del ps, vs_p, vo_p
+    F = System(*dims, device=device, arith="fast")
+    F.set_velocity(*field); F.set_particles(pos0, vel0)
+    F.particles(dt)
+    pf = F.get_particles()[0]
+    F.close()
+    rel = np.max(np.abs(pf.astype(np.float64) - po) / np.maximum(np.abs(po), 1.0), axis=1)
+    flips = int((rel > 1e-6).sum())
+    out["fast_arith"] = {"pos_rel_median": float(np.median(rel)), "pos_rel_max_without_flips": float(rel[rel <= 1e-6].max()) if flips < len(rel) else None,
+                         "clamp_flips": flips, "flip_budget": max(2, len(rel) // 50000)}
+    out["bit_exact_phases"] = exact
+    out["tolerances"] = {"projected_vel_rel": 1e-5, "pos_rel": 1e-6}
+    out["ok"] = bool(out["dt_equal"] and all(exact.values()) and out["projected_vel_rel"] < 1e-5 and out["div_ok"] and out["pos_rel"] <= 1e-6
+                     and flips <= out["fast_arith"]["flip_budget"])
+    O.close()
+    return out
+
+
 def parity_block(args, H):
     """N > 1: the distributed System (y-slabs + particle shards, peer-memory exchanges) against a single-GPU System of the same
     small problem, from identical seeded input, phase by phase: stencil phases and particles bit-exact, projected velocity
@@ -721,6 +783,7 @@ def main():
             "per_kernel": per_kernel}
 
     cpu = None
+    parity = None
     if args.cpu_steps > 0 and world == 1:
         sample_n = min(n, args.cpu_particles)
         u, v, w = S.get_velocity()
@@ -729,6 +792,11 @@ def main():
                "sample": f"{args.cpu_steps} System::solve steps after 1 warm-up step of the same workload ({sample_n} particles, grid {dims}) "
                          f"from the GPU's developed velocity field; OpenMP oracle port on {threads} threads, exact DST Poisson solve",
                "ms_per_step": sec * 1e3, "mac_cell_steps_per_s": ncell / sec}
+        if not args.no_parity:
+            # parity AT THE SIZE THAT IS TIMED, from the very state the timed loop left behind
+            pp, pv = S.get_particles()
+            parity = full_size_parity(dims, u, v, w, pp, pv, device=local, label=f"{args.config}: ")
+            del pp, pv
         del u, v, w
 
     launches_per_step = (int(st1.kernel_launches - st0.kernel_launches)) / n_solves
@@ -768,6 +836,8 @@ def main():
         torch.cuda.empty_cache()
     if world > 1 and not args.no_parity:
         line["parity"] = parity_block(args, H)
+    elif parity is not None:
+        line["parity"] = parity
     if args.config == "c3" and not args.no_c4 and not args.particles:
         # BASELINE configs[3]: 256^3 grid, 100 M particles, y-slab sharded over the same N GPUs, total problem FIXED
         line["c4"] = nested_solve_block(args, H, "c4", True, max(args.c4_steps, 3))
