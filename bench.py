@@ -226,7 +226,9 @@ def run_reference_arm(args, cfg, rank, world):
     sample = (f"{args.steps} {'updateParticles sweeps' if sweep else 'System::solve steps'} of the WHOLE {world}-GPU workload: grid "
               f"{dims[0]}x{dims[1]}x{dims[2]}, {sample_n} of {n} particles ({cfg['cloud']})"
               f"{'' if scale == 1 else ' — value counts the sampled particles only'}; "
-              f"{'compiled reference, 1 thread (it has no threading)' if use_ref else f'OpenMP oracle port on {cores} threads (omp_get_max_threads), exact DST Poisson solve'}")
+              f"{'compiled reference, 1 thread (it has no threading)' if use_ref else f'OpenMP oracle port on {cores} threads (omp_get_max_threads), exact DST Poisson solve'}"
+              f"; flow steps timed: {args.warmup + 1}..{args.warmup + args.steps} from rest (the GPU arm times a later, developed stretch of the same flow; "
+              f"the CPU step cost does not depend on it: direct solve, no iterations)")
     line = {
         "impl": "reference", "metric": "particle_rk2_updates_per_s", "value": val, "unit": "particle-updates/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
@@ -629,12 +631,15 @@ def main():
     ms_step = ms_total / n_solves
     value = n / (ms_step * 1e-3)
     # phase split (CUDA events recorded inside ink_step on the library's stream): median over a few extra steps
-    ph_runs = []
+    ph_runs, ph_iters = [], []
     for _ in range(9):
         S.solve(RENDER_DT)
         ph_runs.append(S.phase_ms())
+        ph_iters.append(int(S.stats().cg_iters))
     phase_acc = {k: float(np.median([p[k] for p in ph_runs])) for k in ph_runs[0]}
-    last_iters = S.stats().cg_iters
+    # the pressure roofline pairs iterations and time of the SAME nine steps (means of both), not the last step's count with a median
+    last_iters = float(np.mean(ph_iters))
+    cg_ms_mean = float(np.mean([p["pressure"] for p in ph_runs])) if "pressure" in ph_runs[0] else 0.0
 
     # ---- e2e: host positions in -> solve -> host positions out, every step ------------------------------
     e2e = None
@@ -745,7 +750,7 @@ def main():
     # ALGORITHM needs on the fine level per iteration (CG pair 10 vector passes + V-cycle 5.25 [trilinear V(1,1)] or 11.5
     # [constant V(2,2)]) x iterations + 16 passes around the solve (RHS, warm start, gradient subtract);
     # the launch-latency-bound coarse levels count against it.  K8 and the stencil phases follow in per_kernel.
-    cg_ms = phase_acc.get("pressure", 0.0)
+    cg_ms = cg_ms_mean
     part_ms = phase_acc.get("particles", 0.0)
     alg_k8 = (9 * rbytes) * n_local + 3 * rbytes * ncell
     traffic_note = None
@@ -778,6 +783,7 @@ def main():
             "traffic_source": "DRAM bytes of one PCG iteration (ncu --set full, profiles/r2_h_top_kernels.txt, C3 on one GPU; not this run) x iterations: "
                               "below the algorithmic bytes because most of the working set stays in L2" if pcg_iter_traffic else None,
             "peak_source": peak_src, "alg_bytes": alg_p, "ms": cg_ms, "cg_iters": last_iters,
+            "pairing": "mean iterations and mean pressure-phase time of the same 9 steps after the timed loop",
             "share_of_step": cg_ms / max(sum(phase_acc.values()), 1e-9),
             "survey_8d": {"bytes_per_cell_per_iter": 44, "frac": (44 * last_iters + 44) * (rbytes / 4) * ncl / max(cg_ms, 1e-9) / 1e6 / peak},
             "per_kernel": per_kernel}
@@ -804,7 +810,9 @@ def main():
     water_ms = sum(phase_acc.get(k, 0.0) for k in ("dt", "advect", "forces", "viscosity", "pressure", "vorticity"))
     line = {
         "metric": "particle_rk2_updates_per_s", "value": value, "unit": "particle-updates/s", "n_gpus": world, "steps": args.steps,
-        "timed_solves": n_solves, "timed_region_ms": ms_total,
+        "timed_solves": n_solves, "timed_region_ms": ms_total, "timed_region_s": ms_total * 1e-3,
+        "steps_note": "`steps` echoes --steps; the device-timed loop ran `timed_solves` whole steps (>= --steps and >= 0.6 s, for clock sampling) "
+                      "and ms_per_step = timed_region_ms / timed_solves",
         "warmup": max(3, args.warmup), "ms_per_step": ms_step, "higher_is_better": True,
         "scaling": "strong" if (world > 1 and args.strong) else "weak", "vs_baseline": None,
         "dtype": args.dtype, "data": "synthetic",
